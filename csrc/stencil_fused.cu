@@ -1,0 +1,359 @@
+// stencil_fused.cu -- halo exchange fused into the stencil sweep, over peer memory.
+//
+// Replaces, from the reference:
+//   boundary_exchange + stencil1d_5          mpi_stencil_gt.cc:83-122,206
+//   boundary_exchange_x/_y + stencil2d_1d_5  mpi_stencil2d_gt.cc:136-373,530-532
+//   (SYCL twins)                             mpi_stencil2d_sycl.cc:212-375, mpi_stencil2d_sycl_oo.cc:363-515
+// and adds the 4-neighbour process-grid exchange of BASELINE config 3.
+//
+// The reference packs strips into staging buffers, hands them to MPI, waits, unpacks, and
+// brackets all of it with device-wide syncs before the stencil may start.  Here one
+// persistent kernel per rank does everything:
+//   phase 1  every CTA stores its share of this rank's boundary values straight into the
+//            neighbours' inboxes (ordinary stores on NVLink-mapped addresses), one
+//            system-scope fence per CTA, then one st.release.sys flag per chunk;
+//   phase 2  CTAs draw tiles from an atomic counter: interior tiles first (they depend on
+//            nobody), boundary tiles last; a boundary tile polls its chunk flags
+//            (ld.acquire.sys, bounded), copies the inbox into the array's own ghost cells
+//            and only then runs the same tile code as the plain kernel.
+// No pack buffer, no MPI/NCCL call, no host synchronisation; flags carry a monotonically
+// increasing epoch and inboxes are double-buffered by epoch parity, so a fast neighbour
+// that is already one launch ahead can never clobber ghosts that are still being read.
+#include <algorithm>
+
+#include "p2p.cuh"
+#include "stencil_tiles.cuh"
+
+namespace gmt {
+
+template <typename RankT>
+__device__ __forceinline__ void load_rank(RankT& dst, const RankT* src)
+{
+  const uint64_t* s = reinterpret_cast<const uint64_t*>(src);
+  uint64_t* d = reinterpret_cast<uint64_t*>(&dst);
+  for (int w = threadIdx.x; w < (int)(sizeof(RankT) / 8); w += blockDim.x) d[w] = s[w];
+  __syncthreads();
+}
+
+// last CTA of this rank: reset the counters and advance the epoch
+__device__ __forceinline__ void finish_epoch(uint32_t* done, uint64_t* epoch, uint64_t e, int n_counters)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int t = atomicAdd(done, 1u);
+    if (t == gridDim.x - 1) {
+      for (int k = 0; k < n_counters; ++k) done[k] = 0u;
+      __threadfence();
+      st_relaxed_sys(epoch, e);
+    }
+  }
+}
+
+// ====================================================================== 1-D
+template <bool kErr>
+__global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d_rank* __restrict__ ranks)
+{
+  __shared__ gmt_halo1d_rank R;
+  __shared__ double red[32];
+  __shared__ int64_t next_tile;
+  load_rank(R, ranks + blockIdx.y);
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int tid = threadIdx.x;
+
+  // 1. push my two boundary values to each neighbour (16 B each) and publish
+  if (blockIdx.x == 0 && (tid == 0 || tid == 32)) {
+    const int s = tid >> 5;  // 0: to the low neighbour, 1: to the high neighbour
+    if (R.has[s]) {
+      const double2 v = ldg128(s == 0 ? R.z + 2 : R.z + R.n);
+      stg128(R.peer_inbox[s][par], v);
+      fence_sys();
+      st_release_sys(R.peer_flag[s], e);
+    }
+  }
+
+  Sten1d S{R.z, R.out, R.n, R.scale, R.x0, R.dx};
+  const int64_t ntiles = (R.n + kTile1d - 1) / kTile1d;
+  // tiles are drawn in order from the counter in done[1]: interior tiles (they depend on
+  // nobody) first, then the edge tiles that need a neighbour's values
+  const int64_t first_int = R.has[0] ? 1 : 0;
+  const int64_t end_int = max(first_int, ntiles - (R.has[1] ? 1 : 0));
+  const int64_t n_int = end_int - first_int;
+  uint32_t* counter = R.done + 1;
+  double err = 0.0;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) next_tile = (int64_t)atomicAdd(counter, 1u);
+    __syncthreads();
+    const int64_t c = next_tile;
+    if (c >= ntiles) break;
+    int64_t t;
+    if (c < n_int) {
+      t = first_int + c;
+    } else {
+      // edge tiles in index order: those below first_int, then those from end_int up
+      const int64_t k = c - n_int;
+      t = k < first_int ? k : end_int + (k - first_int);
+    }
+    const bool lo = (t == 0 && R.has[0]), hi = (t == ntiles - 1 && R.has[1]);
+    if (lo || hi) {
+      // wait for the neighbour, land the ghosts in the array, then compute like any tile
+      if (tid == 0 || tid == 32) {
+        const int s = tid >> 5;
+        if ((s == 0 && lo) || (s == 1 && hi)) {
+          if (!wait_flag_ge(R.my_flag[s], e, R.spin_limit)) atomicExch(R.status, 1u + s);
+          const double2 v = ld_peer_f64x2(R.my_inbox[s][par]);
+          stg128(s == 0 ? R.z : R.z + R.n + 2, v);
+        }
+      }
+      __syncthreads();
+    }
+    tile1d<kErr>(S, t * kTile1d, tid, err);
+  }
+  // 4. epilogue: error norm, then advance the epoch once every CTA of this rank is done
+  if (kErr) {
+    const double part = block_sum(err, red);
+    double total;
+    if (grid_sum_last_block(part, R.err_scratch, red, total, gridDim.x, blockIdx.x)) {
+      if (tid == 0) *R.err_sumsq = total;
+    }
+  }
+  finish_epoch(R.done, R.epoch, e, 2);
+}
+
+// ====================================================================== 2-D
+struct TileMap {
+  int64_t tiles_i, tiles_j, a0, a1, b0, b1, ni, nj, n_int;
+};
+
+// counter value -> tile, interior tiles first, boundary tiles after them
+__device__ __forceinline__ void decode_tile(const TileMap& M, int64_t c, int64_t& ti, int64_t& tj)
+{
+  if (c < M.n_int) {
+    tj = M.b0 + c / M.ni;
+    ti = M.a0 + c % M.ni;
+    return;
+  }
+  int64_t k = c - M.n_int;
+  if (M.n_int == 0) {
+    tj = k / M.tiles_i;
+    ti = k % M.tiles_i;
+    return;
+  }
+  const int64_t nbot = M.b0 * M.tiles_i, ntop = (M.tiles_j - M.b1) * M.tiles_i;
+  if (k < nbot) {
+    tj = k / M.tiles_i;
+    ti = k % M.tiles_i;
+  } else if (k < nbot + ntop) {
+    k -= nbot;
+    tj = M.b1 + k / M.tiles_i;
+    ti = k % M.tiles_i;
+  } else {
+    k -= nbot + ntop;
+    const int64_t nside = M.tiles_i - M.ni;
+    tj = M.b0 + k / nside;
+    const int64_t idx = k % nside;
+    ti = idx < M.a0 ? idx : M.a1 + (idx - M.a0);
+  }
+}
+
+template <int GX, int GY, bool kErr>
+__global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
+{
+  constexpr int TJ = tile_j<GY>();
+  __shared__ gmt_halo2d_rank R;
+  __shared__ double red[32];
+  __shared__ int64_t next_tile;
+  load_rank(R, ranks + blockIdx.y);
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int tid = threadIdx.x;
+  const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
+  TileMap M;
+  M.tiles_i = (nx + kTileI - 1) / kTileI;
+  M.tiles_j = (ny + TJ - 1) / TJ;
+  M.a0 = (GX && R.has[0]) ? 1 : 0;
+  M.a1 = max(M.a0, M.tiles_i - ((GX && R.has[1]) ? 1 : 0));
+  M.b0 = (GY && R.has[2]) ? 1 : 0;
+  M.b1 = max(M.b0, M.tiles_j - ((GY && R.has[3]) ? 1 : 0));
+  M.ni = M.a1 - M.a0;
+  M.nj = M.b1 - M.b0;
+  M.n_int = M.ni * M.nj;
+  const int64_t ntiles = M.tiles_i * M.tiles_j;
+
+  // ---------------- phase 1: export boundary chunks.  x faces: kFlagCols columns x 2 rows
+  // (strided 16-byte pieces gathered into a contiguous inbox); y faces: kTileI rows x 2 columns.
+  const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
+  const int64_t nfy = GY ? M.tiles_i : 0;
+  const int64_t nunits = 2 * (nfx + nfy);
+  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+    int side;
+    int64_t c;
+    if (u < 2 * nfx) {
+      side = (int)(u / nfx);
+      c = u % nfx;
+    } else {
+      side = 2 + (int)((u - 2 * nfx) / nfy);
+      c = (u - 2 * nfx) % nfy;
+    }
+    if (!R.has[side]) continue;
+    double* box = R.peer_inbox[side][par];
+    if (side < 2) {
+      const int64_t j0 = c * kFlagCols;
+      const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
+      double2 v[kFlagCols / kStThreads];
+#pragma unroll
+      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) v[q] = ldg128(src + j * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) stg128(box + 2 * j, v[q]);
+      }
+    } else {
+      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+      const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
+      double2 v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0 && blockIdx.x < nunits) {
+    fence_sys();
+    for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+      const int side = u < 2 * nfx ? (int)(u / nfx) : 2 + (int)((u - 2 * nfx) / nfy);
+      const int64_t c = u < 2 * nfx ? u % nfx : (u - 2 * nfx) % nfy;
+      if (R.has[side]) st_release_sys(R.peer_flag[side] + c, e);
+    }
+  }
+
+  // ---------------- phase 2: tiles from the shared counter
+  Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
+  uint32_t* counter = R.done + 1;
+  double err = 0.0;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) next_tile = (int64_t)atomicAdd(counter, 1u);
+    __syncthreads();
+    const int64_t c = next_tile;
+    if (c >= ntiles) break;
+    int64_t ti, tj;
+    decode_tile(M, c, ti, tj);
+    const int64_t i0 = ti * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+    const int64_t j0 = tj * TJ, j1 = min(ny, j0 + (int64_t)TJ);
+    int sides = 0;
+    if (GX && ti == 0 && R.has[0]) sides |= 1;
+    if (GX && ti == M.tiles_i - 1 && R.has[1]) sides |= 2;
+    if (GY && tj == 0 && R.has[2]) sides |= 4;
+    if (GY && tj == M.tiles_j - 1 && R.has[3]) sides |= 8;
+    if (sides) {
+      if (tid < 4 && ((sides >> tid) & 1)) {
+        const uint64_t* f = R.my_flag[tid] + (tid < 2 ? j0 / kFlagCols : ti);
+        if (!wait_flag_ge(f, e, R.spin_limit)) atomicExch(R.status, 1u + tid);
+      }
+      __syncthreads();
+      if (sides & 3) {
+        for (int64_t j = j0 + tid; j < j1; j += kStThreads) {
+          double* col = R.z + (j + GY) * ldz;
+          if (sides & 1) stg128(col, ld_peer_f64x2(R.my_inbox[0][par] + 2 * j));
+          if (sides & 2) stg128(col + nx + 2, ld_peer_f64x2(R.my_inbox[1][par] + 2 * j));
+        }
+      }
+      if (sides & 12) {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          for (int64_t i = i0 + 2 * tid; i < i1; i += 2 * kStThreads) {
+            if (sides & 4) stg128(R.z + (i + GX) + r * ldz, ld_peer_f64x2(R.my_inbox[2][par] + r * nx + i));
+            if (sides & 8)
+              stg128(R.z + (i + GX) + (ny + 2 + r) * ldz, ld_peer_f64x2(R.my_inbox[3][par] + r * nx + i));
+          }
+        }
+      }
+      __syncthreads();
+    }
+    tile2d<GX, GY, kErr>(S, i0, j0, j1, tid, err);
+  }
+  if (kErr) {
+    const double part = block_sum(err, red);
+    double total;
+    if (grid_sum_last_block(part, R.err_scratch, red, total, gridDim.x, blockIdx.x)) {
+      if (tid == 0) *R.err_sumsq = total;
+    }
+  }
+  finish_epoch(R.done, R.epoch, e, 2);
+}
+
+template <typename RankT>
+static int launch_fused(const void* kernel, const RankT* ranks_dev, int n_ranks, int64_t ntiles,
+                        cudaStream_t st)
+{
+  int grid = 0;
+  int rc = persistent_grid(kernel, kStThreads, ntiles, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev};
+  if (n_ranks > 1) {
+    // several ranks spin on one another inside one launch: co-residency must be guaranteed
+    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(kStThreads), args, 0, st));
+  } else {
+    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(kStThreads), args, 0, st));
+  }
+  return 0;
+}
+
+}  // namespace gmt
+
+extern "C" {
+
+int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, int with_err,
+                            gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n > 0, GMT_EINVAL, "gmt_fused_stencil1d_f64: bad argument");
+  GMT_REQUIRE(n % 2 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil1d_f64: n must be even (16-byte halo stores)");
+  const void* k = with_err ? (const void*)fused1d_kernel<true> : (const void*)fused1d_kernel<false>;
+  return launch_fused(k, ranks_dev, n_ranks, (n + kTile1d - 1) / kTile1d, as_stream(stream));
+}
+
+int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
+                            int gx, int gy, int with_err, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && nx > 0 && ny > 0, GMT_EINVAL, "gmt_fused_stencil2d_f64: bad argument");
+  GMT_REQUIRE((gx == 0 || gx == 2) && (gy == 0 || gy == 2) && (gx || gy), GMT_EINVAL,
+              "gmt_fused_stencil2d_f64: ghost widths must be 0 or 2 and not both 0");
+  GMT_REQUIRE(nx % 4 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil2d_f64: nx must be a multiple of 4");
+  const void* k = nullptr;
+  const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
+  int64_t nt = 0;
+  if (gx && !gy) {
+    k = with_err ? (const void*)fused2d_kernel<2, 0, true> : (const void*)fused2d_kernel<2, 0, false>;
+    nt = tiles_i * ((ny + kTileJx - 1) / kTileJx);
+  } else if (!gx && gy) {
+    k = with_err ? (const void*)fused2d_kernel<0, 2, true> : (const void*)fused2d_kernel<0, 2, false>;
+    nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
+  } else {
+    k = with_err ? (const void*)fused2d_kernel<2, 2, true> : (const void*)fused2d_kernel<2, 2, false>;
+    nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
+  }
+  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream));
+}
+
+int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny)
+{
+  if (side < 2) return (ny + gmt::kFlagCols - 1) / gmt::kFlagCols;
+  return (nx + gmt::kTileI - 1) / gmt::kTileI;
+}
+
+}  // extern "C"

@@ -1,0 +1,278 @@
+/*
+ * gmt_b200.h -- C ABI of libgmt_b200.so, the sm_100a native layer of the
+ * B200 distributed-array / halo-exchange runtime.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, a positive cudaError_t value when
+ *     a CUDA call failed, or a negative GMT_E* code for argument errors;
+ *     gmt_last_error() returns a thread-local message for the last failure.
+ *   - pointers are device pointers unless the name says host; `stream` is a
+ *     cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - all 2-D arrays are COLUMN-MAJOR (first index fastest), the layout the
+ *     reference uses (mpi_stencil2d_sycl.cc:40-43): element (i,j) of an array
+ *     with leading dimension ld lives at i + j*ld.
+ *   - nothing here calls MPI or NCCL.  Cross-GPU traffic is plain loads/stores
+ *     (or multimem.*) on peer-mapped addresses supplied by the caller.
+ */
+#ifndef GMT_B200_H
+#define GMT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* gmt_stream_t;
+
+enum {
+  GMT_OK = 0,
+  GMT_EINVAL = -1,    /* bad argument (size, alignment, enum) */
+  GMT_ETOOBIG = -2,   /* size beyond a documented maximum */
+  GMT_EUNSUPPORTED = -3,
+  GMT_ETIMEOUT = -4   /* an in-kernel bounded spin expired (peer never signalled) */
+};
+
+enum { GMT_SPACE_DEVICE = 0, GMT_SPACE_MANAGED = 1, GMT_SPACE_PINNED = 2 };
+
+/* ------------------------------------------------------------------ errors */
+const char* gmt_last_error(void);
+int gmt_version(void);
+
+/* ------------------------------------------- runtime / device introspection
+ * Replaces set_rank_device (mpi_daxpy.cc:36-62), device_get_vendor_id
+ * (mpi_stencil_gt.cc:151-152), cudaMemGetInfo report (mpi_daxpy_nvtx.cc:201-205)
+ * and the PTRINFO / MEMINFO helpers (cuda_error.h:66-136).                  */
+typedef struct {
+  char name[256];
+  uint64_t total_global_mem;
+  int pci_domain, pci_bus, pci_device;
+  int sm_count, cc_major, cc_minor;
+  int clock_khz, mem_clock_khz, l2_bytes;
+  int managed_memory, concurrent_managed_access;
+  int max_smem_optin;
+  unsigned char uuid[16];
+} gmt_device_props;
+
+int gmt_device_count(int* count);
+int gmt_set_device(int dev);
+int gmt_get_device(int* dev);
+int gmt_device_props_get(int dev, gmt_device_props* out);
+int gmt_mem_info(uint64_t* free_bytes, uint64_t* total_bytes);
+/* type: 0 unregistered, 1 host, 2 device, 3 managed, -1 NULL (cuda_error.h:66-96) */
+int gmt_ptr_info(const void* p, int* type, int* device);
+/* loc: -3 not a CUDA pointer, -2 unmanaged, -1 CPU, >=0 device id, -4 invalid
+ * (cuda_error.h:99-136) */
+int gmt_mem_preferred_location(const void* p, size_t bytes, int* loc);
+int gmt_can_access_peer(int dev, int peer, int* ok);
+int gmt_enable_peer_access(int peer);
+int gmt_device_synchronize(void);
+int gmt_stream_synchronize(gmt_stream_t stream);
+
+/* ------------------------------------------------------------ memory spaces
+ * device / managed / pinned-host allocation (mpi_daxpy_nvtx.cc:177-199) and
+ * CUDA-IPC export so peers can map a device allocation.                     */
+int gmt_alloc(int space, size_t bytes, void** out);
+int gmt_free(int space, void* p);
+/* kind: 0 H2H, 1 H2D, 2 D2H, 3 D2D, 4 default */
+int gmt_memcpy_async(void* dst, const void* src, size_t bytes, int kind, gmt_stream_t stream);
+int gmt_memset_async(void* dst, int value, size_t bytes, gmt_stream_t stream);
+int gmt_ipc_get_handle(void* dev_ptr, unsigned char handle[64]);
+int gmt_ipc_open_handle(const unsigned char handle[64], void** out);
+int gmt_ipc_close_handle(void* mapped);
+
+/* --------------------------------------------------- tracing (daxpy_nvtx.cu:65-105,
+ * mpi_daxpy_nvtx.cc:167-328): NVTX push/pop ranges + profiler capture window */
+int gmt_nvtx_push(const char* name);
+int gmt_nvtx_pop(void);
+int gmt_profiler_start(void);
+int gmt_profiler_stop(void);
+
+/* ---------------------------------------------------------- local fp64 ops */
+/* bytes of zero-initialised scratch every reduction-type entry point needs;
+ * the same scratch may be reused by back-to-back calls on ONE stream.       */
+size_t gmt_reduce_scratch_bytes(void);
+
+/* y <- a*x + y   (replaces cublasDaxpy, mpi_daxpy_nvtx.cc:245) */
+int gmt_daxpy_f64(int64_t n, double a, const double* x, double* y, gmt_stream_t stream);
+/* y <- a*x + y and *out_sum <- sum(y_new), one pass over memory
+ * (replaces daxpy + D2H + host loop, mpi_daxpy_nvtx.cc:245-268) */
+int gmt_daxpy_sum_f64(int64_t n, double a, const double* x, double* y, double* out_sum,
+                      void* scratch, gmt_stream_t stream);
+/* *out <- sum(x)  (host loops mpi_daxpy_nvtx.cc:253-256,296-298) */
+int gmt_sum_f64(int64_t n, const double* x, double* out, void* scratch, gmt_stream_t stream);
+/* *out <- sum((a-b)^2)  (gt::sum_squares mpi_stencil_gt.cc:222; diff_norm
+ * mpi_stencil2d_sycl.cc:165-181).  Caller takes the sqrt.                   */
+int gmt_sumsq_diff_f64(int64_t n, const double* a, const double* b, double* out, void* scratch,
+                       gmt_stream_t stream);
+/* 2-D variant on strided column-major views: sum over (i<nx, j<ny) of (a(i,j)-b(i,j))^2 */
+int gmt_sumsq_diff2d_f64(int64_t nx, int64_t ny, const double* a, int64_t lda, const double* b,
+                         int64_t ldb, double* out, void* scratch, gmt_stream_t stream);
+/* axis sum of a column-major (nx,ny,ld) array: axis 0 -> out[j]=sum_i z(i,j), j<n_out;
+ * axis 1 -> out[i]=sum_j z(i,j), i<n_out  (gt::sum_axis_to mpi_stencil2d_gt.cc:611,620) */
+int gmt_axis_sum_f64(int64_t nx, int64_t ny, int64_t ld, const double* z, int axis, int64_t n_out,
+                     double* out, gmt_stream_t stream);
+/* x[:] <- value  (fill ctor mpi_stencil2d_gt.cc:598) */
+int gmt_fill_f64(int64_t n, double value, double* x, gmt_stream_t stream);
+/* x[i] <- (start + i*step)*mul   -- daxpy initialisers (mpi_daxpy_nvtx.cc:209-212) */
+int gmt_iota_f64(int64_t n, double start, double step, double mul, double* x, gmt_stream_t stream);
+
+/* 5-point 4th-order first derivative, out[i] = scale * sum_k c_k in[i+k], k=0..4
+ * (stencil1d_5, mpi_stencil_gt.cc:54-59).  in has n+4 elements.
+ * variant: 0 = one thread per point (mirrors a generic expression kernel),
+ *          1 = 256-bit vectorised streaming kernel,
+ *          2 = TMA bulk-copy (cp.async.bulk + mbarrier) pipelined kernel.    */
+int gmt_stencil1d_f64(int64_t n, const double* in, double* out, double scale, int variant,
+                      gmt_stream_t stream);
+/* same stencil applied along dim 0 (contiguous) or dim 1 (strided) of a column-major
+ * 2-D array.  dim 0: z is (nx+4, ny) with ldz >= nx+4; dim 1: z is (nx, ny+4) with
+ * ldz >= nx.  dz is (nx, ny) with lddz >= nx.
+ * (stencil2d_1d_5_d0/_d1, mpi_stencil2d_gt.cc:84-110)                        */
+int gmt_stencil2d_f64(int dim, int64_t nx, int64_t ny, const double* z, int64_t ldz, double* dz,
+                      int64_t lddz, double scale, int variant, gmt_stream_t stream);
+/* cross stencil on a (nx+4, ny+4) array ghosted in both dims:
+ * out(i,j) = sx * d/dx + sy * d/dy   (BASELINE config 3, no reference counterpart) */
+int gmt_stencil2d_xy_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,
+                         int64_t ldo, double sx, double sy, gmt_stream_t stream);
+
+/* strided 2-D block copy dst(i,j) = src(i,j), i<rows (contiguous), j<cols: the pack /
+ * unpack kernel of the baseline exchange (mpi_stencil2d_gt.cc:166,172,239,251;
+ * buf_from_view / buf_to_view mpi_stencil2d_sycl.cc:82-116)                  */
+int gmt_copy2d_f64(int64_t rows, int64_t cols, const double* src, int64_t ld_src, double* dst,
+                   int64_t ld_dst, gmt_stream_t stream);
+
+/* analytic initialisers, device side (host loops mpi_stencil_gt.cc:177-196,
+ * mpi_stencil2d_gt.cc:445-497).
+ * 1-D: y[g] = x^3 for every g in [0, n+2*nb) with x = x0 + (g-nb)*dx (so ghosts get the
+ *      analytic continuation; the caller overwrites interior-facing ghosts by exchange),
+ *      optional actual[i] = 3x^2.                                            */
+int gmt_init_stencil1d_f64(int64_t n, int nb, double x0, double dx, double* y, double* actual,
+                           int fill_left_ghost, int fill_right_ghost, gmt_stream_t stream);
+/* 2-D: z(i,j) = x^3 + y^2 on the ghosted array (gx, gy ghost widths per dim), ghost cells
+ *      filled analytically only on the sides whose bit is set in ghost_mask
+ *      (1 = low x, 2 = high x, 4 = low y, 8 = high y), others set to `poison`.
+ *      deriv_mode: 0 none, 1 actual = 3x^2, 2 actual = 2y, 3 actual = sx*3x^2 + sy*2y     */
+int gmt_init_stencil2d_f64(int64_t nx, int64_t ny, int gx, int gy, double x0, double y0, double dx,
+                           double dy, double* z, int64_t ldz, double* actual, int64_t lda,
+                           int deriv_mode, double sx, double sy, int ghost_mask, double poison,
+                           gmt_stream_t stream);
+
+/* ===================================================================== fused
+ * halo exchange + stencil kernels over peer memory.
+ *
+ * One (virtual) rank's view of an exchange.  A launch takes an array of these in DEVICE
+ * memory and blockIdx.y selects the entry: a production process passes ONE entry whose
+ * peer_* pointers are NVLink mappings of the neighbours' memory, while single-GPU
+ * emulation passes every rank's entry in one cooperative launch (peers are then other
+ * buffers on the same GPU).
+ *
+ * Protocol: each launch is epoch e = *epoch + 1.  A rank stores its boundary values into
+ * the neighbour's inbox[e & 1] with ordinary stores, fences at system scope and publishes e
+ * in the neighbour's flag word for that chunk (st.release.sys).  The consumer polls the
+ * flag (ld.acquire.sys, bounded), copies the inbox into its own in-array ghost cells --
+ * so after the kernel the array looks exactly as it does after the reference's
+ * boundary_exchange -- and computes the boundary tiles last, interior tiles first.
+ * A side with has == 0 is a physical boundary: its ghost cells are used as they are.    */
+typedef struct {
+  double* z;            /* n + 4 doubles, 32-byte aligned */
+  double* out;          /* n doubles, 32-byte aligned */
+  int64_t n;
+  double scale;
+  int32_t has[2];       /* 0 = low neighbour, 1 = high neighbour */
+  double* my_inbox[2][2];   /* [side][parity] -> 2 doubles each, local memory */
+  double* peer_inbox[2][2]; /* [side][parity] -> the neighbour's my_inbox[1-side][parity] */
+  uint64_t* my_flag[2];     /* one word per side */
+  uint64_t* peer_flag[2];   /* the neighbour's my_flag[1-side] */
+  uint64_t* epoch;      /* device-resident epoch counter of this rank */
+  uint32_t* done;       /* >= 2 zero-initialised words: CTA completion + tile counters (self-resetting) */
+  uint32_t* status;     /* set non-zero when a bounded spin expired */
+  void* err_scratch;    /* optional: gmt_reduce_scratch_bytes() of zeroed scratch */
+  double* err_sumsq;    /* optional: receives sum((out - 3x^2)^2), x = x0 + i*dx */
+  double x0, dx;
+  int64_t spin_limit;   /* 0 = default */
+} gmt_halo1d_rank;
+
+/* replaces boundary_exchange + stencil1d_5 (mpi_stencil_gt.cc:83-122,206) */
+int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, int with_err,
+                            gmt_stream_t stream);
+
+/* 2-D: sides 0 = low x (dim 0), 1 = high x, 2 = low y (dim 1), 3 = high y.
+ * gx, gy in {0, 2} are the ghost widths of z in each dim; z is (nx+2gx, ny+2gy) and
+ * out(i,j) = sx * d/dx (if gx) + sy * d/dy (if gy).  gx=2,gy=0 is the reference's dim-0
+ * slab test, gx=0,gy=2 its dim-1 test (boundary_exchange_x/_y + stencil2d_1d_5_d0/_d1,
+ * mpi_stencil2d_gt.cc:136-373,530-532); gx=gy=2 is the 4-neighbour process-grid case of
+ * BASELINE config 3.  Inbox layouts: x sides hold 2 doubles per column (inbox[2*j + r]),
+ * y sides hold two contiguous ghost columns (inbox[r*nx + i]).                        */
+typedef struct {
+  double* z;
+  double* out;
+  int64_t nx, ny, ldz, ldo;
+  int32_t gx, gy;
+  double sx, sy;
+  int32_t has[4];
+  double* my_inbox[4][2];
+  double* peer_inbox[4][2];
+  uint64_t* my_flag[4];     /* gmt_halo2d_flag_count(side, nx, ny) words per side */
+  uint64_t* peer_flag[4];
+  uint64_t* epoch;
+  uint32_t* done;
+  uint32_t* status;
+  void* err_scratch;
+  double* err_sumsq;        /* optional: sum((out - (sx*3x^2*[gx] + sy*2y*[gy]))^2) */
+  double x0, y0, dx, dy;
+  int64_t spin_limit;
+} gmt_halo2d_rank;
+
+int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
+                            int gx, int gy, int with_err, gmt_stream_t stream);
+/* flag words needed on `side` for the given interior extents */
+int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
+
+/* Collectives written as kernels over peer memory.  `bufs_dev`/`flags_dev` are device
+ * arrays of world pointers (one per rank, index = rank), all ranks call with the same
+ * epoch sequence.  A rank-local state block carries the epoch.                 */
+typedef struct {
+  int32_t rank, world;
+  double** peer_buf;       /* device array [world]: peer-mapped base of each rank's buffer */
+  uint64_t** peer_flag;    /* device array [world]: peer-mapped flag block of each rank (>= world*8 words) */
+  double* mc_buf;          /* multicast VA of the buffer, or NULL */
+  uint64_t* epoch;         /* device-resident epoch counter (this rank) */
+  uint32_t* done;
+  uint32_t* status;
+  void* scratch;           /* local reduce scratch (gmt_reduce_scratch_bytes) */
+  int64_t spin_limit;
+} gmt_coll_rank;
+
+/* in-place allgather: rank r's slice [r*n,(r+1)*n) of its own buffer is stored into the same
+ * offset of every peer's buffer (MPI_Allgather(MPI_IN_PLACE), mpi_daxpy_nvtx.cc:285,
+ * mpigatherinplace.f90:39).  src == NULL means in place; otherwise the slice is read from
+ * src (mpi_daxpy_nvtx.cc:288).  use_multicast: store through mc_buf (multimem.st).   */
+int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, const double* const* src_dev,
+                      int use_multicast, gmt_stream_t stream);
+/* gather to root in place (MPI_Gather(MPI_IN_PLACE), BASELINE config 5) */
+int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int root,
+                   gmt_stream_t stream);
+/* in-place sum all-reduce of a vector of n doubles living at offset `off` of every rank's
+ * buffer (MPI_Allreduce(MPI_IN_PLACE), mpi_stencil2d_gt.cc:615,624).
+ * algo: 0 = one-shot P2P read, 1 = two-shot P2P, 2 = multimem.ld_reduce one-shot     */
+int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int64_t off, int algo,
+                      gmt_stream_t stream);
+/* fused daxpy + global sum: y <- a x + y on each rank, every rank's out_sum <- sum over all
+ * ranks of sum(y)  (mpi_daxpy_nvtx.cc:245-310 collapsed).  The rank partial goes through slot
+ * `off` (doubles) of the symmetric buffer: [off + r] for r < world.               */
+int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, double a,
+                            const double* const* x_dev, double* const* y_dev, double* const* out_dev,
+                            int64_t off, gmt_stream_t stream);
+/* axis sum whose epilogue all-reduces the n_out-vector in place at `off` of the symmetric
+ * buffer (gt::sum_axis_to + MPI_Allreduce, mpi_stencil2d_gt.cc:611-625)              */
+int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
+                               int64_t ld, const double* const* z_dev, int axis, int64_t n_out,
+                               int64_t off, gmt_stream_t stream);
+/* signal barrier across ranks (MPI_Barrier, mpi_daxpy_nvtx.cc:277) */
+int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GMT_B200_H */
