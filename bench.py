@@ -1,0 +1,183 @@
+#!/usr/bin/env python
+"""Flagship benchmark (driver contract).
+
+    python bench.py --gpus N --steps K --warmup W            (N=1)
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric (BASELINE.json): stencil GLUP/s on the "2D fp64 stencil, 16384x16384 per GPU, 2D
+decomposition with 4-neighbor ghost exchange" config, weak scaling, one fused halo+stencil
+kernel per GPU per step.  A step = exchange the 2-wide ghost faces with the (up to) four
+neighbours over NVLink peer memory AND apply out = d/dx + d/dy (5-point, 4th order) to the
+whole 16384^2 tile, plus the in-kernel error norm against the analytic derivative.
+`value` is the whole-job aggregate GLUP/s (lattice updates / s over all GPUs), timed on the
+device with CUDA events, max over ranks.  The input (2 GiB) and output (2 GiB) per GPU exceed
+the 126 MB L2, so no L2 flush is needed between iterations.
+
+`e2e` runs the same step through the public API `Stencil2DWorkload.step_e2e()`: every step
+uploads the physical-boundary ghost values from pinned host memory, runs the fused kernel and
+reads the error norm back to the host.
+
+Extra keys (`extra`) report the other BASELINE configs at the same N: 1-D stencil GLUP/s,
+daxpy+global-sum GB/s, exposed halo-exchange microseconds.
+
+`--impl reference` reports why the unmodified reference cannot run here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+REFERENCE_UNAVAILABLE = ("bd4/gpu-mpi-tests is a flat directory of C++/CUDA/Fortran/SYCL programs with no setup.py/pyproject "
+                         "(pip: 'not installable'); its stencil programs need MPI + gtensor (fetched from GitHub by CPM) "
+                         "or SYCL, none of which exist on this image")
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="fused", choices=["fused", "baseline", "reference"])
+    ap.add_argument("--n", type=int, default=16384, help="per-GPU tile edge (BASELINE config: 16384)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary configs")
+    return ap.parse_args()
+
+
+def main() -> int:
+    args = parse()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
+        return 0
+
+    import torch
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.parallel import runtime
+    from gpu_mpi_tests_b200.utils import timing
+
+    warmup = max(args.warmup, 3)
+    rt = runtime.init()
+    if not rt.is_cuda:
+        raise SystemExit("bench.py needs a CUDA device")
+    if rt.world_size != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={rt.world_size}: launch with torchrun --nproc-per-node {args.gpus}")
+    n = args.n
+    wl = Stencil2DWorkload(rt, n, n, mode="grid", impl=args.impl, with_err=True)
+    wl.setup()
+    wl.step()
+    torch.cuda.synchronize()
+    wl.check()
+    err0 = max(wl.err_norm(r) for r in wl.ranks)
+
+    # ---- device-timed region: K fused steps
+    sampler = timing.ClockSampler(rt.device.index)
+    sampler.start()
+    t = timing.time_steps(wl.step, args.steps, warmup, rt.device)
+    clocks = sampler.stop()
+    wl.check()
+    points = n * n * rt.world_size
+    glups = points / (t["ms_per_step"] * 1e-3) / 1e9
+
+    # ---- end to end through the public API: H2D boundary values + step + D2H error norm
+    h2d, d2h = wl.e2e_bytes()
+    te = timing.time_steps(wl.step_e2e, args.steps, warmup, rt.device)
+    e2e_glups = points / (te["ms_per_step"] * 1e-3) / 1e9
+    err1 = rt.reduce_scalar(max(wl.err_norm(r) for r in wl.ranks), "max")
+
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:  # noqa: BLE001
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    per_gpu_gbs = 16.0 * n * n / (t["ms_per_step"] * 1e-3) / 1e9
+
+    extra = {}
+    if not args.no_extra:
+        extra = secondary(rt, args, warmup)
+
+    rec = {
+        "metric": "stencil2d_glups",
+        "value": glups,
+        "unit": "GLUP/s",
+        "n_gpus": rt.world_size,
+        "steps": args.steps,
+        "warmup": warmup,
+        "ms_per_step": t["ms_per_step"],
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "fp64",
+        "data": "synthetic (analytic field z = x^3 + y^2, device-initialised)",
+        "impl": args.impl,
+        "config": {
+            "model": "2D fp64 5-point stencil d/dx+d/dy with 4-neighbour ghost exchange",
+            "per_gpu_tile": [n, n],
+            "global_points": points,
+            "parallelism": f"grid{wl.px}x{wl.py}",
+            "l2": "inputs larger than L2 (2 GiB in + 2 GiB out per GPU), no flush",
+            "peer_memory": getattr(getattr(wl, "space", None), "kind", "n/a"),
+        },
+        "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
+                   "reasons": clocks.get("reasons", []), "samples": clocks.get("samples", 0),
+                   "power_w_max": clocks.get("power_w_max")},
+        "e2e": {"value": e2e_glups, "unit": "GLUP/s", "ms_per_step": te["ms_per_step"],
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": args.steps * wl.launches_per_step,
+        "roofline": {"hbm_gbs_per_gpu": per_gpu_gbs, "frac_of_measured_copy_peak": per_gpu_gbs / hbm,
+                     "measured_copy_peak_gbs": hbm},
+        "err_norm_max": max(err0, err1),
+        "extra": extra,
+    }
+    if rt.rank == 0:
+        print(json.dumps(rec))
+    runtime.finalize()
+    return 0
+
+
+def secondary(rt, args, warmup: int) -> dict:
+    """The other BASELINE configs at this N (short runs)."""
+    import torch
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.parallel.halo import FusedStencil1D
+    from gpu_mpi_tests_b200.parallel.symm import make_space
+    from gpu_mpi_tests_b200.utils import timing
+    out = {}
+    steps = max(5, min(args.steps, 20))
+    W = rt.world_size
+    try:
+        space = make_space(rt)
+        # 1-D stencil, 2^27 points per GPU (BASELINE config 2)
+        n1 = 1 << 27
+        p1 = FusedStencil1D(space, n1, with_err=False)
+        p1.init_analytic()
+        t = timing.time_steps(p1.step, steps, warmup, rt.device)
+        p1.check_status()
+        out["stencil1d_2p27_glups"] = n1 * W / (t["ms_per_step"] * 1e-3) / 1e9
+        out["stencil1d_ms_per_step"] = t["ms_per_step"]
+        del p1
+        torch.cuda.empty_cache()
+        # reference-default 2-D slab tiles (1024 x 524288 per rank), dim 0 and dim 1
+        for mode, (nx, ny) in (("dim0", (1024, 524288)), ("dim1", (524288, 1024))):
+            wl = Stencil2DWorkload(rt, nx, ny, mode=mode, impl="fused", with_err=False, space=space)
+            wl.setup()
+            t = timing.time_steps(wl.step, steps, warmup, rt.device)
+            wl.check()
+            out[f"stencil2d_ref_{mode}_glups"] = nx * ny * W / (t["ms_per_step"] * 1e-3) / 1e9
+            out[f"stencil2d_ref_{mode}_ms_per_step"] = t["ms_per_step"]
+            del wl
+            torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001 - secondary numbers must not sink the headline
+        out["error"] = repr(e)
+    return out
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,164 @@
+"""2-D stencil workload: the framework's flagship "model".
+
+One object owns a rank's share of a 2-D fp64 field z = x^3 + y^2 on [0,8)^2, decomposed either
+as the reference does (slabs along the differentiated dim, mpi_stencil2d_gt.cc:385-572) or on a
+2-D process grid with four face neighbours (BASELINE config 3), and advances it by "steps":
+
+    step()      exchange ghosts with the neighbours and apply the 5-point derivative(s)
+                -- ONE fused kernel launch (parallel/halo.py), or the library-only baseline
+                (baseline/exchange.py + un-fused kernels) when impl="baseline";
+    step_e2e()  what a time-stepping user calls: upload this step's physical-boundary values
+                from pinned host memory, step(), read the error norm back to the host.
+
+The CPU/gloo flavour (no GPU) runs the same API on torch CPU tensors with the baseline
+exchange.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..ops import local
+from ..parallel import decomp
+from ..parallel import runtime as _rt
+from ..parallel.halo import FusedStencil2D
+from ..parallel.symm import PeerSpace, make_space
+
+F64 = torch.float64
+DOMAIN = 8.0
+
+
+class Stencil2DWorkload:
+    def __init__(self, rt: "_rt.Runtime | None" = None, nx: int = 16384, ny: int = 16384, mode: str = "grid",
+                 impl: str = "fused", with_err: bool = True, space: PeerSpace | None = None,
+                 grid: tuple | None = None, stage: str = "none", mem_space: str = "device",
+                 spin_limit: int = 0):
+        """mode: 'grid' (gx=gy=2, px x py ranks), 'dim0' (gx=2, world x 1), 'dim1' (gy=2, 1 x world).
+        nx, ny: per-rank interior extents (weak scaling)."""
+        self.rt = rt or _rt.current()
+        self.mode, self.impl, self.with_err = mode, impl, with_err
+        world = space.world if space is not None else self.rt.world_size
+        if mode == "grid":
+            self.px, self.py = grid if grid is not None else decomp.best_grid(world)
+            self.gx = self.gy = 2
+        elif mode == "dim0":
+            self.px, self.py, self.gx, self.gy = world, 1, 2, 0
+        elif mode == "dim1":
+            self.px, self.py, self.gx, self.gy = 1, world, 0, 2
+        else:
+            raise ValueError("mode must be grid, dim0 or dim1")
+        self.nx, self.ny = nx, ny
+        self.device = self.rt.device if space is None else space.device
+        self.stage, self.mem_space = stage, mem_space
+        self.launches_per_step = 1
+        if impl == "fused":
+            if self.device.type != "cuda":
+                raise RuntimeError("impl='fused' needs CUDA; use impl='baseline' on the CPU/gloo path")
+            self.space = space if space is not None else make_space(self.rt)
+            self.plan = FusedStencil2D(self.space, self.px, self.py, nx, ny, self.gx, self.gy, with_err=with_err,
+                                       spin_limit=spin_limit)
+            self.ranks = self.plan.ranks
+            self.z, self.out = self.plan.z, self.plan.out
+            self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy
+        elif impl == "baseline":
+            from ..baseline.exchange import BaselineStencil2D
+            self.plan = BaselineStencil2D(self.rt, self.px, self.py, nx, ny, self.gx, self.gy, stage=stage,
+                                          mem_space=mem_space)
+            self.ranks = [self.rt.rank]
+            self.z, self.out = self.plan.z, self.plan.out
+            self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy
+            self.launches_per_step = self.plan.launches_per_step
+        else:
+            raise ValueError("impl must be fused or baseline")
+        self._host_bc = None
+        self._err_host = None
+        self._dev_bc = None
+
+    # ------------------------------------------------------------------ setup / step
+    def setup(self, poison: float = 0.0) -> None:
+        self.plan.init_analytic(poison=poison)
+
+    def step(self) -> None:
+        self.plan.step()
+
+    def points_per_rank(self) -> int:
+        return self.nx * self.ny
+
+    def hbm_bytes_per_step(self) -> int:
+        """Algorithmic HBM traffic per rank: read z once, write out once."""
+        return 16 * self.nx * self.ny
+
+    # ------------------------------------------------------------------ end to end
+    def _prepare_e2e(self) -> None:
+        """Pinned host copies of this rank's physical-boundary ghost values (the per-step input)
+        and a pinned scalar for the per-step result."""
+        self._host_bc, self._dev_bc = {}, {}
+        pin = self.device.type == "cuda"
+        for r in self.ranks:
+            g = decomp.Grid2D(self.px, self.py, r)
+            z = self.z[r]
+            gx, gy, nx, ny = self.gx, self.gy, self.nx, self.ny
+            views = {}
+            if gx and g.neighbour(0) < 0:
+                views[0] = z[gy:gy + ny, 0:2]
+            if gx and g.neighbour(1) < 0:
+                views[1] = z[gy:gy + ny, gx + nx:gx + nx + 2]
+            if gy and g.neighbour(2) < 0:
+                views[2] = z[0:2, gx:gx + nx]
+            if gy and g.neighbour(3) < 0:
+                views[3] = z[gy + ny:gy + ny + 2, gx:gx + nx]
+            for side, v in views.items():
+                h = torch.empty(v.shape, dtype=F64, pin_memory=pin)
+                h.copy_(v)
+                self._host_bc[(r, side)] = (h, v)
+                if side < 2 and self.device.type == "cuda":
+                    self._dev_bc[(r, side)] = torch.empty(v.shape, dtype=F64, device=self.device)
+        self._err_host = {r: torch.zeros(1, dtype=F64, pin_memory=pin) for r in self.ranks}
+
+    def e2e_bytes(self) -> tuple[int, int]:
+        """(host->device, device->host) bytes per step, counted from the tensors copied."""
+        if self._host_bc is None:
+            self._prepare_e2e()
+        h2d = sum(h.numel() * 8 for (h, _v) in self._host_bc.values())
+        d2h = 8 * len(self.ranks)
+        return h2d, d2h
+
+    def step_e2e(self) -> float:
+        """Upload boundary values, run the step, read the error norm back.  Returns the largest
+        err_norm over the ranks hosted by this process (host float: synchronises)."""
+        if self._host_bc is None:
+            self._prepare_e2e()
+        for (r, side), (h, v) in self._host_bc.items():
+            if side < 2 and (r, side) in self._dev_bc:
+                # strided 2-wide strip: contiguous H2D into staging, then the unpack kernel
+                d = self._dev_bc[(r, side)]
+                d.copy_(h, non_blocking=True)
+                local.copy2d(d, v)
+            else:
+                v.copy_(h, non_blocking=True)
+        self.step()
+        worst = 0.0
+        for r in self.ranks:
+            self._err_host[r].copy_(self.err_sumsq(r), non_blocking=True)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().synchronize()
+        for r in self.ranks:
+            worst = max(worst, float(self._err_host[r].item()) ** 0.5)
+        return worst
+
+    # ------------------------------------------------------------------ validation
+    def analytic(self, rank: int) -> torch.Tensor:
+        return self.plan.analytic(rank)
+
+    def err_sumsq(self, rank: int) -> torch.Tensor:
+        """Device scalar sum((numeric-analytic)^2): from the fused kernel's epilogue when the plan
+        computes it, else from the device reduction kernel."""
+        if self.impl == "fused" and self.with_err:
+            return self.plan.err_sumsq(rank)
+        return local.sumsq_diff(self.out[rank], self.analytic(rank))
+
+    def err_norm(self, rank: int) -> float:
+        return float(self.err_sumsq(rank).item()) ** 0.5
+
+    def check(self) -> None:
+        if hasattr(self.plan, "check_status"):
+            self.plan.check_status()

@@ -1,0 +1,234 @@
+"""CPU unit tests (no GPU, no process group): decomposition arithmetic, rank->device mapping
+incl. the error message, slice normalisation, stencil math against closed forms, closed-form
+sums, golden output strings."""
+import math
+
+import pytest
+import torch
+
+from gpu_mpi_tests_b200.ops import local
+from gpu_mpi_tests_b200.parallel import array as ga
+from gpu_mpi_tests_b200.parallel import decomp, runtime
+from gpu_mpi_tests_b200.utils import oracle, report
+
+F64 = torch.float64
+
+
+# ------------------------------------------------------------------ rank -> device
+def test_rank_device_mapping_identity_and_oversubscription():
+    assert runtime.map_rank_to_device(4, 3, 8) == (3, 1)
+    # 42 procs on 6 GPUs (daxpy.cu:6-7): 7 consecutive ranks share a device
+    assert [runtime.map_rank_to_device(42, r, 6)[0] for r in (0, 6, 7, 41)] == [0, 0, 1, 5]
+    assert runtime.map_rank_to_device(42, 0, 6)[1] == 7
+
+
+def test_rank_device_mapping_error_message():
+    with pytest.raises(runtime.RankDeviceError) as e:
+        runtime.map_rank_to_device(7, 0, 6)
+    assert str(e.value) == "ERROR: Number of ranks (7) not a multiple of number of GPUs (6)"
+
+
+def test_vendor_id_packing():
+    assert runtime.pack_vendor_id(0, 0x1B, 0) == 0x00001B00
+    assert report.err_norm_line(1, 4, 1, runtime.pack_vendor_id(1, 0xAB, 3), 0.5) == \
+        "1/4 [1:0x0001ab03] err_norm = 0.50000000"
+
+
+def test_world_of_one_runtime(monkeypatch):
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    rt = runtime.init(use_cuda=False)
+    assert (rt.world_size, rt.rank, rt.node_count, rt.distributed) == (1, 0, 1, False)
+    assert rt.reduce_scalar(3.5) == 3.5
+    assert rt.rank_device_line().startswith("RANK[1/1] => DEVICE[1/1] mem=")
+    rt.barrier()
+    runtime.finalize()
+
+
+# ------------------------------------------------------------------ decomposition
+def test_slab_decomposition():
+    s = decomp.Slab1D(32 * 1024 * 1024, 8, 3)
+    assert (s.n_local, s.n_local_with_ghost, s.start, s.lo, s.hi) == (4 * 1024 * 1024, 4 * 1024 * 1024 + 4,
+                                                                      12 * 1024 * 1024, 2, 4)
+    assert decomp.Slab1D(64, 4, 0).lo == -1 and decomp.Slab1D(64, 4, 3).hi == -1
+    with pytest.raises(decomp.DecompositionError) as e:
+        decomp.Slab1D(33554432, 3, 2)
+    assert str(e.value) == "2 nmpi (3) must be divisor of domain size (33554432), exiting"
+    assert decomp.weak_slab(1024, 4, 1).n_global == 4096
+
+
+def test_grid_decomposition():
+    assert decomp.best_grid(8) == (4, 2) and decomp.best_grid(4) == (2, 2) and decomp.best_grid(2) == (2, 1)
+    assert decomp.best_grid(1) == (1, 1) and decomp.best_grid(6) == (3, 2)
+    g = decomp.Grid2D(4, 2, 5)
+    assert (g.cx, g.cy) == (1, 1)
+    assert g.neighbours() == [4, 6, 1, -1]
+    assert g.physical_mask() == 8
+    assert decomp.Grid2D(1, 1, 0).physical_mask() == 15
+    assert decomp.slab_as_grid(0, 4, 2).neighbours() == [1, 3, -1, -1]
+    assert decomp.slab_as_grid(1, 4, 0).neighbours() == [-1, -1, -1, 1]
+    # every face is shared symmetrically
+    for r in range(8):
+        g = decomp.Grid2D(4, 2, r)
+        for s in range(4):
+            nb = g.neighbour(s)
+            if nb >= 0:
+                assert decomp.Grid2D(4, 2, nb).neighbour(s ^ 1) == r
+
+
+# ------------------------------------------------------------------ slices / arrays
+def test_slice_normalisation_rules():
+    """mpi_stencil2d_sycl_oo.cc:174-181: negatives count from the end, end == 0 means to-end."""
+    assert ga.normalize_slice(2, 4, 12) == (2, 4)
+    assert ga.normalize_slice(-4, -2, 12) == (8, 10)
+    assert ga.normalize_slice(-2, 0, 12) == (10, 12)
+    assert ga.normalize_slice(0, 2, 12) == (0, 2)
+    with pytest.raises(IndexError):
+        ga.normalize_slice(5, 3, 12)
+    with pytest.raises(IndexError):
+        ga.normalize_slice(0, 13, 12)
+
+
+def test_array2d_is_column_major_and_slice_copies():
+    """The 6x6(+ghost) pattern of the reference's disabled test_buf_view
+    (mpi_stencil2d_sycl.cc:118-159): recognisable values through pack and unpack."""
+    n, nb = 6, 2
+    a = ga.Array2D(n + 2 * nb, n, device=torch.device("cpu"))
+    for col in range(n):
+        for row in range(n + 2 * nb):
+            a.set(row, col, 100.0 * row + col)
+    assert a(3, 4) == 304.0
+    assert a.t[4, 3] == 304.0 and a.t.stride(1) == 1  # first index fastest
+    with pytest.raises(IndexError):
+        a(n + 2 * nb, 0)
+    sbuf = ga.Array2D(nb, n, device=torch.device("cpu"))
+    ga.copy_src_slice(a, sbuf, 0, nb, 2 * nb)            # rows [2,4): left interior boundary
+    assert sbuf(0, 5) == 205.0 and sbuf(1, 0) == 300.0
+    ga.copy_src_slice(a, sbuf, 0, -2 * nb, -nb)          # rows [6,8): right interior boundary
+    assert sbuf(0, 1) == 601.0
+    ga.copy_dest_slice(sbuf, a, 0, -nb, 0)               # into the right ghost rows [8,10)
+    assert a(8, 1) == 601.0 and a(9, 2) == 702.0
+    cbuf = ga.Array2D(n + 2 * nb, 2, device=torch.device("cpu"))
+    ga.copy_src_slice(a, cbuf, 1, -2, 0)                 # last two columns
+    assert cbuf(3, 1) == 305.0
+    with pytest.raises(ValueError):
+        ga.copy_src_slice(a, cbuf, 0, 0, 2)
+
+
+def test_memory_spaces_on_cpu():
+    for space in ga.SPACES:
+        t = ga.zeros((3, 4), space, torch.device("cpu"))
+        assert t.shape == (3, 4) and t.dtype == F64 and float(t.sum()) == 0.0
+    with pytest.raises(ValueError):
+        ga.empty(4, "texture")
+    assert float(ga.full(5, math.pi, device=torch.device("cpu")).sum()) == pytest.approx(5 * math.pi)
+
+
+# ------------------------------------------------------------------ math
+def test_daxpy_closed_forms():
+    x, y = oracle.daxpy_init_small(1024)
+    local.daxpy(2.0, x, y)
+    assert float(y.sum()) == oracle.daxpy_small_expected_sum(1024) == 524800.0
+    assert report.daxpy_sum(float(y.sum())) == "SUM = 524800.000000"
+    n = 1 << 20
+    x, y = oracle.daxpy_init_scaled(n)
+    s = local.daxpy_sum(2.0, x, y)
+    assert float(s) == pytest.approx(oracle.daxpy_scaled_expected_sum(n), rel=1e-12)
+    assert report.rank_sum(0, 2, 524288.5) == "0/2 SUM = 524288.500000"
+    assert report.rank_allsum(1, 2, oracle.daxpy_scaled_expected_allsum(n, 2)) == "1/2 ALLSUM = 1048577.000000"
+
+
+def test_stencil_is_exact_for_cubics_and_err_norm_is_roundoff():
+    n, world = 1 << 16, 4
+    total = 0.0
+    ys = [oracle.init_stencil1d(n, r, world) for r in range(world)]
+    for r in range(world):  # oracle exchange
+        y = ys[r][0]
+        if r > 0:
+            y[:2] = ys[r - 1][0][-4:-2]
+        if r < world - 1:
+            y[-2:] = ys[r + 1][0][2:4]
+    for r in range(world):
+        y, act, scale = ys[r]
+        e = oracle.err_norm(local.stencil1d(y, scale), act)
+        assert e < oracle.err_norm_pass_bound(n)
+        total += e
+    assert total < 1e-5
+    # a stale ghost cell is unmistakable
+    y, act, scale = oracle.init_stencil1d(n, 1, world)
+    assert oracle.err_norm(local.stencil1d(y, scale), act) > 1e4
+
+
+@pytest.mark.parametrize("dim", [0, 1])
+def test_stencil2d_oracle_single_rank(dim):
+    z, act, scale = oracle.init_stencil2d(64, 48, dim, 0, 1)
+    e = oracle.err_norm(local.stencil2d(z, dim, scale), act)
+    assert e < 1e-8
+    out = local.stencil2d(z, dim, scale, variant="generic")
+    assert out.shape == act.shape
+
+
+def test_cpu_init_helpers_match_oracle():
+    n, world = 512, 3
+    for r in range(world):
+        y_ref, act_ref, _ = oracle.init_stencil1d(n, r, world)
+        y = torch.empty(n + 4, dtype=F64)
+        act = torch.empty(n, dtype=F64)
+        dx = 8.0 / (n * world)
+        local.init_stencil1d(y, act, n, r * n * dx, dx, r == 0, r == world - 1)
+        assert torch.allclose(y, y_ref, rtol=0, atol=1e-12) and torch.allclose(act, act_ref, rtol=0, atol=1e-12)
+    z = torch.empty(10 + 4, 8 + 4, dtype=F64)
+    act = torch.empty(10, 8, dtype=F64)
+    local.init_stencil2d(z, act, 8, 10, 2, 2, 0.0, 0.0, 0.5, 0.25, 3, 2.0, 4.0, 1 | 8, -7.0)
+    assert float(z[5, 0]) == pytest.approx((-1.0) ** 3 + (0.75) ** 2)   # low-x ghost analytic
+    assert float(z[5, 11]) == -7.0                                      # high-x ghost poisoned
+    assert float(z[0, 5]) == -7.0 and float(z[13, 5]) == pytest.approx(1.5 ** 3 + 2.75 ** 2)
+    assert float(z[0, 0]) == -7.0                                       # corner never analytic
+    assert float(act[2, 3]) == pytest.approx(2.0 * 3 * 1.5 ** 2 + 4.0 * 2 * 0.5)
+
+
+def test_gather_closed_form():
+    n = 1000
+    for r in range(6):
+        assert float(oracle.gather_slot_values(r, n).sum()) == oracle.gather_slot_sum(r, n)
+    assert oracle.gather_all_sum(4, n) == sum(float(oracle.gather_slot_values(r, n).sum()) for r in range(4))
+
+
+def test_axis_sum_and_reductions_cpu():
+    z = torch.rand(7, 5, dtype=F64)
+    assert torch.allclose(local.axis_sum(z, 0), z.sum(dim=1))
+    assert torch.allclose(local.axis_sum(z, 1, n_out=3), z.sum(dim=0)[:3])
+    a, b = torch.rand(100, dtype=F64), torch.rand(100, dtype=F64)
+    assert local.diff_norm(a, b) == pytest.approx(float(((a - b) ** 2).sum()) ** 0.5)
+    assert float(local.total(a)) == pytest.approx(float(a.sum()))
+
+
+# ------------------------------------------------------------------ golden strings
+def test_golden_output_strings():
+    assert report.rank_device(0, 4, 0, 8, 191_000_000_000) == "RANK[1/4] => DEVICE[1/8] mem=191000000000"
+    assert report.memory_per_core(None) == "MEMORY_PER_CORE is not set"
+    assert report.memory_per_core("4096") == "MEMORY_PER_CORE=4096"
+    assert report.rank_sum_gt(2, 4, 2, 0x1B00, 524800.0) == "2/4 [2:0x00001b00] SUM = 524800.000000"
+    assert report.daxpy_nvtx_banner(1, 8, 6291456, 50331648) == "1 nodes, 8 ranks, 6291456 elements each, total 50331648"
+    assert report.gpu_memory(1 << 30, 2 << 30) == "GPU memory 1024.000 / 2048.000 (1024.000) MB"
+    assert report.time_line(3, 8, "total", 1.23456) == "3/8 TIME total  : 1.235"
+    assert report.time_line(3, 8, "kernel", 0.001) == "3/8 TIME kernel : 0.001"
+    assert report.time_line(3, 8, "barrier", 0.0) == "3/8 TIME barrier: 0.000"
+    assert report.time_line(3, 8, "gather", 0.5) == "3/8 TIME gather : 0.500"
+    assert report.meminfo("d_x", -2) == "CUDA PreferredLocation of 'd_x' is UNMANAGED"
+    assert report.meminfo("m_x", 0) == "CUDA PreferredLocation of 'm_x' is DEVICE (0)"
+    assert report.meminfo("m_x", -1) == "CUDA PreferredLocation of 'm_x' is CPU (-1)"
+    assert report.meminfo("h", -3) == "CUDA PreferredLocation of 'h' is NOT CUDA"
+    assert report.stencil1d_banner(8, 33554432, 4194304) == ["n procs  = 8", "n_global = 33554432", "n_local  = 4194304"]
+    assert report.exchange_time_s(0, 2, 0.000123) == "0/2 exchange time 0.00012300"
+    assert report.stencil2d_banner(4, 4096, 524288, 1000, 10)[1:3] == ["n_global_deriv = 4096", "n_global_other = 524288"]
+    assert report.test_deriv_line(0, "device", True, 1.5, 2e-7) == "TEST dim:0, device , buf:1; 1.50000000, err=0.00000020"
+    assert report.test_deriv_line(1, "managed", False, 0.25, 0.0) == "TEST dim:1, managed, buf:0; 0.25000000, err=0.00000000"
+    assert report.test_sum_line(1, "device", 0.003) == "TEST dim:1, device , buf:0; allreduce=0.00300000"
+    assert report.oo_exchange_time(1, 0.5) == "1: exchange time 0.50000000 ms"
+    assert report.oo_err_norm(1, 0x8086, 1e-6) == "1: [0x00008086] err_norm = 0.00000100"
+    assert report.dev_bytes(8.6e9).endswith("GB") and report.dev_bytes(5e6).endswith("MB")
+    assert report.cuda_error("x.cu", 12, "malloc", 2, "out of memory") == "x.cu(12): CUDA Error (malloc) 2: out of memory"
+    assert report.mpi_error("f.cc", 35, 13) == "f.cc:35 error 13"
+    assert "MEMORY_PER_CORE=" in report.mpienv_line(3, 4096)
+    assert report.sycl_banner(2, 0, 524288, 2048, 1024, 100, 5, False)[-1] == "stage_host = 0"

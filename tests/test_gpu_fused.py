@@ -1,0 +1,127 @@
+"""The fused halo-exchange + stencil kernels, all ranks emulated on one GPU in a single
+cooperative launch (VirtualSpace): protocol correctness (flags, epochs, parity double
+buffering), ghost landing, fused error norm -- against the analytic derivative and against
+the un-fused kernels fed with an oracle-exchanged array."""
+import pytest
+import torch
+
+from gpu_mpi_tests_b200.ops import local
+from gpu_mpi_tests_b200.parallel.halo import FusedStencil1D, FusedStencil2D
+from gpu_mpi_tests_b200.parallel.symm import VirtualSpace
+
+pytestmark = pytest.mark.gpu
+F64 = torch.float64
+
+
+def close(a, b, rtol=1e-10):
+    """Same arithmetic, separately compiled kernels: equal up to FMA-contraction round-off,
+    which the 1/dx scale amplifies -- compare relative to the field's magnitude."""
+    return float((a - b).abs().max()) <= rtol * (float(b.abs().max()) + 1.0)
+
+
+@pytest.mark.parametrize("world,n", [(1, 4096), (2, 64), (3, 1000), (4, 8192), (8, 65536), (5, 4096 * 3 + 2)])
+def test_fused_stencil1d(dev, world, n):
+    plan = FusedStencil1D(VirtualSpace(world, dev), n, with_err=True, spin_limit=1 << 24)
+    plan.init_analytic()
+    for r in plan.ranks:  # interior-facing ghosts must come from the neighbour, not from init
+        if r > 0:
+            plan.z[r][:2] = 1e30
+        if r < world - 1:
+            plan.z[r][-2:] = 1e30
+    steps = 5
+    for _ in range(steps):
+        plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [steps] * world
+    xs = torch.arange(n * world, dtype=F64, device=dev) * plan.dx
+    for r in plan.ranks:
+        act = 3 * xs[r * n:(r + 1) * n] ** 2
+        assert float((plan.out[r] - act).abs().max()) < 1e-6
+        assert plan.err_norm(r) == pytest.approx(float(((plan.out[r] - act) ** 2).sum()) ** 0.5, rel=1e-6, abs=1e-12)
+        # ghosts landed in the array: same state as after the reference's boundary_exchange
+        if r > 0:
+            assert torch.equal(plan.z[r][:2], plan.z[r - 1][-4:-2])
+        if r < world - 1:
+            assert torch.equal(plan.z[r][-2:], plan.z[r + 1][2:4])
+        # identical to the plain kernel on the exchanged array
+        # (not bit-identical: the two kernels are compiled separately and may contract FMAs differently)
+        assert close(plan.out[r], local.stencil1d(plan.z[r], plan.scale))
+
+
+CASES_2D = [
+    # px, py, nx, ny, gx, gy
+    (1, 1, 2048, 512, 2, 2),
+    (4, 1, 1024, 256, 2, 0),     # reference dim-0 slab test
+    (2, 1, 4096, 100, 2, 0),     # several row tiles per column
+    (3, 1, 64, 3000, 2, 0),      # several flag chunks per face
+    (1, 4, 2048, 256, 0, 2),     # reference dim-1 slab test
+    (1, 3, 1024, 130, 0, 2),
+    (2, 2, 2048, 256, 2, 2),     # BASELINE config 3 shape: 4 neighbours
+    (4, 2, 1024, 384, 2, 2),
+    (3, 2, 36, 50, 2, 2),
+]
+
+
+@pytest.mark.parametrize("px,py,nx,ny,gx,gy", CASES_2D)
+def test_fused_stencil2d(dev, px, py, nx, ny, gx, gy):
+    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, gx, gy, with_err=True, spin_limit=1 << 24)
+    plan.init_analytic(poison=1e30)
+    steps = 4
+    for _ in range(steps):
+        plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [steps] * (px * py)
+    for r in plan.ranks:
+        act = plan.analytic(r)
+        assert float((plan.out[r] - act).abs().max()) < 1e-6, f"rank {r}"
+        assert plan.err_norm(r) == pytest.approx(float(((plan.out[r] - act) ** 2).sum()) ** 0.5, rel=1e-6, abs=1e-12)
+        z = plan.z[r]
+        if gx and gy:
+            ref = local.stencil2d_xy(z, plan.sx, plan.sy)
+        elif gx:
+            ref = local.stencil2d(z, 0, plan.sx)
+        else:
+            ref = local.stencil2d(z, 1, plan.sy)
+        assert close(plan.out[r], ref)
+
+
+def test_fused_values_change_between_steps(dev):
+    """Parity double buffering: the array changes every step; ghosts must track it."""
+    plan = FusedStencil2D(VirtualSpace(4, dev), 2, 2, 1024, 128, 2, 2, with_err=False, spin_limit=1 << 24)
+    plan.init_analytic(poison=1e30)
+    for it in range(6):
+        for r in plan.ranks:
+            plan.z[r][2:-2, 2:-2] += float(it + 1)  # interior only; ghosts refreshed by the exchange
+        plan.step()
+        torch.cuda.synchronize()
+        for r in plan.ranks:
+            g = plan.grids[r]
+            if g.neighbour(0) >= 0:
+                assert torch.equal(plan.z[r][2:-2, :2], plan.z[g.neighbour(0)][2:-2, -4:-2])
+            if g.neighbour(3) >= 0:
+                assert torch.equal(plan.z[r][-2:, 2:-2], plan.z[g.neighbour(3)][2:4, 2:-2])
+    plan.check_status()
+
+
+def test_fused_without_err_and_world_of_one_matches_plain(dev):
+    plan = FusedStencil2D(VirtualSpace(1, dev), 1, 1, 4096, 300, 2, 2, with_err=False)
+    plan.init_analytic()
+    plan.step()
+    torch.cuda.synchronize()
+    assert close(plan.out[0], local.stencil2d_xy(plan.z[0], plan.sx, plan.sy))
+
+
+def test_dead_neighbour_times_out_instead_of_hanging(dev):
+    """Rank 0 believes it has a high neighbour that never launches: the bounded spin must expire
+    and be reported, not hang the GPU."""
+    from gpu_mpi_tests_b200.parallel.halo import HaloTimeout
+    plan = FusedStencil1D(VirtualSpace(2, dev), 8192, with_err=False, spin_limit=2000)
+    plan.init_analytic()
+    # launch only rank 0's entry: its neighbour's flag never arrives
+    from gpu_mpi_tests_b200.ops._lib import lib
+    lib.gmt_fused_stencil1d_f64(plan._ranks_dev.data_ptr(), 1, plan.n, 0, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    with pytest.raises(HaloTimeout):
+        plan.check_status()
