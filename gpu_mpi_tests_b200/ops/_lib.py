@@ -108,6 +108,9 @@ _SIGS = {
     "gmt_reduce_scratch_bytes": (C.c_size_t, []),
     "gmt_daxpy_f64": (None, [c_i64, c_dbl, c_ptr, c_ptr, c_ptr]),
     "gmt_daxpy_sum_f64": (None, [c_i64, c_dbl, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "gmt_daxpy_sum_noalloc_f64": (None, [c_i64, c_dbl, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "gmt_noalloc_max_n": (c_i64, []),
+    "gmt_noalloc_scratch_bytes": (C.c_size_t, []),
     "gmt_sum_f64": (None, [c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gmt_sumsq_diff_f64": (None, [c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gmt_sumsq_diff2d_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr]),

@@ -100,6 +100,25 @@ int gmt_daxpy_f64(int64_t n, double a, const double* x, double* y, gmt_stream_t 
  * (replaces daxpy + D2H + host loop, mpi_daxpy_nvtx.cc:245-268) */
 int gmt_daxpy_sum_f64(int64_t n, double a, const double* x, double* y, double* out_sum,
                       void* scratch, gmt_stream_t stream);
+/* Same result as gmt_daxpy_sum_f64 for callers that cannot allocate device memory.
+ * (No counterpart in the reference.)  Meant for programs whose own arrays or memory pool
+ * already fill the GPU, so a late cudaMalloc can fail, and for time-stepping loops where an
+ * allocator call -- which may synchronise the whole device -- is not acceptable.  The scratch
+ * is a fixed array inside the library image (gmt_noalloc_scratch_bytes() = 64.25 KiB, resident
+ * on every GPU that loads the library until the process exits); the caller passes inputs and
+ * outputs only, and nothing in the call allocates or frees.
+ *   - n is limited to gmt_noalloc_max_n() = 33,554,432 elements (one partial per
+ *     4096-element chunk must fit the array); larger n returns GMT_ETOOBIG.
+ *   - The first call on each device looks up the array's device address; make that first
+ *     call before any stream capture.
+ *   - All calls on a device share the array, which keeps the previous call's contents; the
+ *     counter that must start at zero is cleared on `stream` by every call.  Calls that overlap
+ *     on the GPU (unordered streams, concurrent host threads) race on it: order them.
+ *   - The partials are added in index order: the sum is bit-reproducible run to run.        */
+int gmt_daxpy_sum_noalloc_f64(int64_t n, double a, const double* x, double* y, double* out_sum,
+                              gmt_stream_t stream);
+int64_t gmt_noalloc_max_n(void);
+size_t gmt_noalloc_scratch_bytes(void);
 /* *out <- sum(x)  (host loops mpi_daxpy_nvtx.cc:253-256,296-298) */
 int gmt_sum_f64(int64_t n, const double* x, double* out, void* scratch, gmt_stream_t stream);
 /* *out <- sum((a-b)^2)  (gt::sum_squares mpi_stencil_gt.cc:222; diff_norm
