@@ -1,0 +1,490 @@
+// collectives.cu -- allgather / gather / all-reduce / barrier and the two fused
+// compute+collective ops (daxpy + global sum, axis-sum + all-reduce) as kernels over
+// NVLink 5 / NVSwitch peer memory.
+//
+// Replaces, from the reference:
+//   MPI_Allgather(MPI_IN_PLACE) / MPI_Allgather   mpi_daxpy_nvtx.cc:285,288; mpigatherinplace.f90:39
+//   MPI_Allreduce(MPI_IN_PLACE, SUM)              mpi_stencil2d_gt.cc:615,624
+//   cublasDaxpy + allgather + host sums           mpi_daxpy_nvtx.cc:245-310  (daxpy_allreduce)
+//   gt::sum_axis_to + MPI_Allreduce               mpi_stencil2d_gt.cc:611-625 (axis_sum_allreduce)
+//   MPI_Barrier                                   mpi_daxpy_nvtx.cc:277
+// and adds the gather-to-root BASELINE config 5 asks for.
+//
+// NVSwitch gives every GPU the same bandwidth to every peer, so nothing here uses rings or
+// trees: data goes straight to its final place (one store per peer, or one multimem.st for
+// all of them), small reductions are one-shot (every rank reads every peer's vector), larger
+// ones two-shot.  Every wait is a bounded spin on a system-scope acquire.
+#include <algorithm>
+
+#include "common.cuh"
+#include "p2p.cuh"
+
+namespace gmt {
+
+constexpr int kCollThreads = 512;
+constexpr int kRoundStride = 32;  // words per signalling round in a flag block
+
+struct CollShared {
+  gmt_coll_rank R;
+  double* buf[GMT_COLL_MAX_WORLD];
+  double* stage[GMT_COLL_MAX_WORLD];
+  uint64_t* flag[GMT_COLL_MAX_WORLD];
+  double red[32];
+  int64_t next;
+  bool last;
+};
+
+__device__ __forceinline__ uint64_t coll_enter(CollShared& S, const gmt_coll_rank* ranks)
+{
+  {
+    const uint64_t* s = reinterpret_cast<const uint64_t*>(ranks + blockIdx.y);
+    uint64_t* d = reinterpret_cast<uint64_t*>(&S.R);
+    for (int w = threadIdx.x; w < (int)(sizeof(gmt_coll_rank) / 8); w += blockDim.x) d[w] = s[w];
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < S.R.world) {
+    S.buf[threadIdx.x] = S.R.peer_buf ? S.R.peer_buf[threadIdx.x] : nullptr;
+    S.stage[threadIdx.x] = S.R.peer_stage ? S.R.peer_stage[threadIdx.x] : nullptr;
+    S.flag[threadIdx.x] = S.R.peer_flag[threadIdx.x];
+  }
+  __syncthreads();
+  return ld_relaxed_sys(S.R.epoch) + 1;
+}
+
+// "rank R.rank has reached `round` of epoch e" to every rank (or to one).  Call after a CTA
+// barrier: the release is cumulative over what the CTA wrote before the barrier.
+__device__ __forceinline__ void signal_all(CollShared& S, int round, uint64_t e)
+{
+  if ((int)threadIdx.x < S.R.world) st_release_sys(S.flag[threadIdx.x] + round * kRoundStride + S.R.rank, e);
+}
+__device__ __forceinline__ void signal_one(CollShared& S, int dst, int round, uint64_t e)
+{
+  if (threadIdx.x == 0) st_release_sys(S.flag[dst] + round * kRoundStride + S.R.rank, e);
+}
+// wait until every rank (or one rank) has signalled `round` of epoch e; ends with a CTA barrier
+__device__ __forceinline__ void wait_all(CollShared& S, int round, uint64_t e)
+{
+  if ((int)threadIdx.x < S.R.world) {
+    if (!wait_flag_ge(S.flag[S.R.rank] + round * kRoundStride + threadIdx.x, e, S.R.spin_limit))
+      atomicExch(S.R.status, 1u + threadIdx.x);
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void wait_one(CollShared& S, int src, int round, uint64_t e)
+{
+  if (threadIdx.x == 0) {
+    if (!wait_flag_ge(S.flag[S.R.rank] + round * kRoundStride + src, e, S.R.spin_limit))
+      atomicExch(S.R.status, 1u + src);
+  }
+  __syncthreads();
+}
+
+// True in exactly one CTA of this rank: the last one to get here.  Everything the other CTAs
+// wrote before is visible (system scope) to whoever synchronises with that CTA afterwards.
+__device__ __forceinline__ bool arrive_last(CollShared& S, uint32_t* counter)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    fence_sys();
+    S.last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+    if (S.last) fence_sys();
+  }
+  __syncthreads();
+  return S.last;
+}
+
+__device__ __forceinline__ void coll_finish(CollShared& S, uint64_t e)
+{
+  if (threadIdx.x == 0) {
+    S.R.done[0] = S.R.done[1] = S.R.done[2] = S.R.done[3] = 0u;
+    __threadfence();
+    st_relaxed_sys(S.R.epoch, e);
+  }
+}
+
+__device__ __forceinline__ void multimem_st_32B(double* mc, const double4_t& v)
+{
+  // the bytes are what matters: 2 x multimem.st.v4.f32 carry 4 doubles to every GPU of the group
+  const float4* f = reinterpret_cast<const float4*>(&v);
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(f[0].x), "f"(f[0].y),
+               "f"(f[0].z), "f"(f[0].w)
+               : "memory");
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + 2), "f"(f[1].x), "f"(f[1].y),
+               "f"(f[1].z), "f"(f[1].w)
+               : "memory");
+}
+
+// ============================================================ allgather / gather
+// root < 0: allgather (everyone receives).  root >= 0: gather to root.
+__global__ void __launch_bounds__(kCollThreads, 2)
+  gather_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n, int from_in, int use_mc, int root)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  const int W = S.R.world, r = S.R.rank;
+  const bool all = root < 0;
+  // round 0: nobody's buffer may be written before its owner has entered this epoch
+  if (blockIdx.x == 0) {
+    if (all) signal_all(S, 0, e);
+    else if (r == root) signal_all(S, 0, e);
+  }
+  if (all) wait_all(S, 0, e);
+  else if (r != root) wait_one(S, root, 0, e);
+
+  const bool sender = all || r != root;
+  if (sender) {
+    double* own = S.buf[r];
+    const double* src = from_in ? S.R.in : own + (int64_t)r * n;
+    const int64_t off = (int64_t)r * n;
+    const bool vec = (n % 4 == 0) && aligned(src, 32) && aligned(own, 32);
+    const int64_t stride = (int64_t)gridDim.x * kCollThreads;
+    const int64_t t0 = (int64_t)blockIdx.x * kCollThreads + threadIdx.x;
+    if (vec) {
+      const int64_t nv = n / 4;
+      for (int64_t v = t0; v < nv; v += 2 * stride) {
+        const bool two = v + stride < nv;
+        const double4_t a = ldg256(src + 4 * v);
+        double4_t b;
+        if (two) b = ldg256(src + 4 * (v + stride));
+        if (all && use_mc) {
+          multimem_st_32B(S.R.mc_buf + off + 4 * v, a);
+          if (two) multimem_st_32B(S.R.mc_buf + off + 4 * (v + stride), b);
+        } else if (all) {
+          for (int p = 0; p < W; ++p) {
+            if (p == r && !from_in) continue;
+            stg256(S.buf[p] + off + 4 * v, a);
+            if (two) stg256(S.buf[p] + off + 4 * (v + stride), b);
+          }
+        } else {
+          stg256(S.buf[root] + off + 4 * v, a);
+          if (two) stg256(S.buf[root] + off + 4 * (v + stride), b);
+        }
+      }
+    } else {
+      for (int64_t i = t0; i < n; i += stride) {
+        const double a = src[i];
+        if (all) {
+          for (int p = 0; p < W; ++p)
+            if (p != r || from_in) S.buf[p][off + i] = a;
+        } else {
+          S.buf[root][off + i] = a;
+        }
+      }
+    }
+  } else if (from_in) {
+    // root of a gather with a separate send buffer keeps its own contribution too
+    double* own = S.buf[r] + (int64_t)r * n;
+    for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kCollThreads)
+      own[i] = S.R.in[i];
+  }
+  // round 1: my slice has landed everywhere; return only when everyone's slice has landed here
+  if (arrive_last(S, S.R.done + 0)) {
+    if (all) {
+      signal_all(S, 1, e);
+      wait_all(S, 1, e);
+    } else if (r != root) {
+      signal_one(S, root, 1, e);
+    } else {
+      if ((int)threadIdx.x < W && (int)threadIdx.x != root) {
+        if (!wait_flag_ge(S.flag[r] + kRoundStride + threadIdx.x, e, S.R.spin_limit))
+          atomicExch(S.R.status, 1u + threadIdx.x);
+      }
+      __syncthreads();
+    }
+    coll_finish(S, e);
+  }
+}
+
+// ============================================================ all-reduce building blocks
+// After this call every rank's input vector of epoch e sits in its staging area and is visible.
+__device__ __forceinline__ void publish_inputs(CollShared& S, uint64_t e)
+{
+  if (arrive_last(S, S.R.done + 0)) signal_all(S, 0, e);
+  wait_all(S, 0, e);
+}
+
+// out[i] = sum over ranks (rank order) of their staged inputs; i in this CTA's share
+template <int kAlgo>
+__device__ __forceinline__ void reduce_tail(CollShared& S, uint64_t e, int64_t n)
+{
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
+  const int64_t cap = S.R.stage_cap;
+  const int64_t in_off = (int64_t)par * cap, res_off = (int64_t)(2 + par) * cap;
+  const int64_t stride = (int64_t)gridDim.x * kCollThreads;
+  const int64_t t0 = (int64_t)blockIdx.x * kCollThreads + threadIdx.x;
+  double* out = S.R.out;
+  if (kAlgo == 0) {
+    for (int64_t i = t0; i < n; i += stride) {
+      double s = 0.0;
+      for (int p = 0; p < W; ++p) s += ld_peer_f64(S.stage[p] + in_off + i);
+      out[i] = s;
+    }
+  } else if (kAlgo == 2) {
+    const double* mc = S.R.mc_stage + in_off;
+    for (int64_t i = t0; i < n; i += stride) out[i] = multimem_ld_reduce_add_f64(mc + i);
+  } else {
+    // two-shot: reduce my slice, store it into everyone's result area, then collect
+    const int64_t lo = n * r / W, hi = n * (r + 1) / W;
+    for (int64_t i = lo + t0; i < hi; i += stride) {
+      double s = 0.0;
+      for (int p = 0; p < W; ++p) s += ld_peer_f64(S.stage[p] + in_off + i);
+      for (int p = 0; p < W; ++p) S.stage[p][res_off + i] = s;
+    }
+    if (arrive_last(S, S.R.done + 1)) signal_all(S, 1, e);
+    wait_all(S, 1, e);
+    const double* res = S.stage[r] + res_off;
+    for (int64_t i = t0; i < n; i += stride) out[i] = ld_peer_f64(res + i);
+  }
+  if (arrive_last(S, S.R.done + 2)) coll_finish(S, e);
+}
+
+template <int kAlgo>
+__global__ void __launch_bounds__(kCollThreads, 2)
+  allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  double* mine = S.stage[S.R.rank] + (int64_t)(e & 1) * S.R.stage_cap;
+  const double* in = S.R.in;
+  for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kCollThreads)
+    mine[i] = in[i];
+  publish_inputs(S, e);
+  reduce_tail<kAlgo>(S, e, n);
+}
+
+// axis sum straight into the staging area, then the all-reduce
+template <int kAlgo>
+__global__ void __launch_bounds__(kCollThreads, 2)
+  axis_sum_allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t nx, int64_t ny, int64_t ld,
+                            int axis, int64_t n_out)
+{
+  __shared__ CollShared S;
+  __shared__ double tile[16][33];
+  const uint64_t e = coll_enter(S, ranks);
+  double* mine = S.stage[S.R.rank] + (int64_t)(e & 1) * S.R.stage_cap;
+  const double* z = S.R.in;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (axis == 0) {
+    // out[j] = sum_i z(i,j): one warp per column, lanes along the contiguous axis
+    const int64_t nwarps = (int64_t)gridDim.x * (kCollThreads / 32);
+    for (int64_t j = (int64_t)blockIdx.x * (kCollThreads / 32) + warp; j < n_out; j += nwarps) {
+      const double* col = z + j * ld;
+      double a0 = 0.0, a1 = 0.0;
+      int64_t i = lane;
+      for (; i + 32 < nx; i += 64) {
+        a0 += col[i];
+        a1 += col[i + 32];
+      }
+      if (i < nx) a0 += col[i];
+      const double s = warp_sum(a0 + a1);
+      if (lane == 0) mine[j] = s;
+    }
+  } else {
+    // out[i] = sum_j z(i,j): 32 rows per CTA trip, the 16 warps split the columns
+    for (int64_t i0 = (int64_t)blockIdx.x * 32; i0 < n_out; i0 += (int64_t)gridDim.x * 32) {
+      const int64_t i = i0 + lane;
+      double acc = 0.0;
+      if (i < n_out)
+        for (int64_t j = warp; j < ny; j += kCollThreads / 32) acc += z[i + j * ld];
+      tile[warp][lane] = acc;
+      __syncthreads();
+      if (warp == 0 && i < n_out) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < kCollThreads / 32; ++k) s += tile[k][lane];
+        mine[i] = s;
+      }
+      __syncthreads();
+    }
+  }
+  publish_inputs(S, e);
+  reduce_tail<kAlgo>(S, e, n_out);
+}
+
+// ============================================================ daxpy + global sum
+constexpr int kDaUnroll = 2;
+constexpr int64_t kDaChunk = (int64_t)kCollThreads * kDaUnroll;
+
+__global__ void __launch_bounds__(kCollThreads, 2)
+  daxpy_allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n, double a)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
+  const double* __restrict__ x = S.R.in;
+  double* __restrict__ y = S.R.y;
+  double acc = 0.0;
+  if (aligned(x, 32) && aligned(y, 32)) {
+    const int64_t n4 = n / 4, nchunks = (n4 + kDaChunk - 1) / kDaChunk;
+    uint32_t* counter = S.R.done + 3;
+    for (;;) {
+      __syncthreads();
+      if (threadIdx.x == 0) S.next = (int64_t)atomicAdd(counter, 1u);
+      __syncthreads();
+      const int64_t c = S.next;
+      if (c >= nchunks) break;
+      double4_t xv[kDaUnroll], yv[kDaUnroll];
+#pragma unroll
+      for (int u = 0; u < kDaUnroll; ++u) {
+        const int64_t i = c * kDaChunk + threadIdx.x + (int64_t)u * kCollThreads;
+        if (i < n4) {
+          xv[u] = ldg256_stream(x + 4 * i);
+          yv[u] = ldg256(y + 4 * i);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kDaUnroll; ++u) {
+        const int64_t i = c * kDaChunk + threadIdx.x + (int64_t)u * kCollThreads;
+        if (i < n4) {
+          yv[u].x = a * xv[u].x + yv[u].x;
+          yv[u].y = a * xv[u].y + yv[u].y;
+          yv[u].z = a * xv[u].z + yv[u].z;
+          yv[u].w = a * xv[u].w + yv[u].w;
+          stg256(y + 4 * i, yv[u]);
+          acc += (yv[u].x + yv[u].y) + (yv[u].z + yv[u].w);
+        }
+      }
+    }
+    if (blockIdx.x == 0) {
+      for (int64_t k = 4 * n4 + threadIdx.x; k < n; k += kCollThreads) {
+        const double v = a * x[k] + y[k];
+        y[k] = v;
+        acc += v;
+      }
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kCollThreads) {
+      const double v = a * x[i] + y[i];
+      y[i] = v;
+      acc += v;
+    }
+  }
+  const double part = block_sum(acc, S.red);
+  double total;
+  if (!grid_sum_last_block(part, S.R.scratch, S.red, total, gridDim.x, blockIdx.x)) return;
+  // last CTA of this rank: one-shot all-reduce of the rank totals
+  if (threadIdx.x == 0) S.stage[r][(int64_t)par * S.R.stage_cap] = total;
+  __syncthreads();
+  signal_all(S, 0, e);
+  wait_all(S, 0, e);
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int p = 0; p < W; ++p) s += ld_peer_f64(S.stage[p] + (int64_t)par * S.R.stage_cap);
+    *S.R.out = s;
+  }
+  coll_finish(S, e);
+}
+
+__global__ void __launch_bounds__(kCollThreads) barrier_kernel(const gmt_coll_rank* __restrict__ ranks)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  signal_all(S, 0, e);
+  wait_all(S, 0, e);
+  coll_finish(S, e);
+}
+
+// ============================================================ launch helpers
+static int coll_grid(const void* kernel, int64_t work_ctas, int n_ranks, int* grid)
+{
+  int occ = 0;
+  GMT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kCollThreads, 0));
+  if (occ < 1) occ = 1;
+  int64_t cap = (int64_t)sm_count() * occ;
+  if (n_ranks > 1) cap /= n_ranks;
+  GMT_REQUIRE(cap >= 1, GMT_ETOOBIG, "too many virtual ranks (%d) for one cooperative launch", n_ranks);
+  *grid = (int)std::max<int64_t>(1, std::min<int64_t>(cap, work_ctas));
+  return 0;
+}
+
+static int coll_launch(const void* kernel, int grid, int n_ranks, void** args, cudaStream_t st)
+{
+  if (n_ranks > 1)
+    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(kCollThreads), args, 0, st));
+  else
+    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(kCollThreads), args, 0, st));
+  return 0;
+}
+
+}  // namespace gmt
+
+extern "C" {
+
+int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int from_in, int use_multicast,
+                      gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_allgather_f64: bad argument");
+  int grid = 0, root = -1;
+  const void* k = (const void*)gather_kernel;
+  int rc = coll_grid(k, (n / 4 + kCollThreads * 2 - 1) / (kCollThreads * 2) + 1, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&from_in, (void*)&use_multicast, (void*)&root};
+  return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int root, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0 && root >= 0, GMT_EINVAL, "gmt_gather_f64: bad argument");
+  int grid = 0, from_in = 0, use_mc = 0;
+  const void* k = (const void*)gather_kernel;
+  int rc = coll_grid(k, (n / 4 + kCollThreads * 2 - 1) / (kCollThreads * 2) + 1, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&from_in, (void*)&use_mc, (void*)&root};
+  return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int algo, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_allreduce_f64: bad argument");
+  GMT_REQUIRE(algo >= 0 && algo <= 2, GMT_EINVAL, "gmt_allreduce_f64: unknown algorithm %d", algo);
+  const void* k = algo == 0 ? (const void*)allreduce_kernel<0>
+                 : algo == 1 ? (const void*)allreduce_kernel<1> : (const void*)allreduce_kernel<2>;
+  int grid = 0;
+  int rc = coll_grid(k, (n + kCollThreads * 4 - 1) / (kCollThreads * 4), n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev, (void*)&n};
+  return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, double a, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_daxpy_allreduce_f64: bad argument");
+  const void* k = (const void*)daxpy_allreduce_kernel;
+  int grid = 0;
+  int rc = coll_grid(k, (n / 4 + kDaChunk - 1) / kDaChunk, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&a};
+  return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny, int64_t ld,
+                               int axis, int64_t n_out, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && nx > 0 && ny > 0 && ld >= nx, GMT_EINVAL,
+              "gmt_axis_sum_allreduce_f64: bad argument");
+  GMT_REQUIRE(axis == 0 || axis == 1, GMT_EINVAL, "gmt_axis_sum_allreduce_f64: axis must be 0 or 1");
+  GMT_REQUIRE(n_out >= 0 && n_out <= (axis == 0 ? ny : nx), GMT_EINVAL,
+              "gmt_axis_sum_allreduce_f64: n_out exceeds the surviving extent");
+  const void* k = (const void*)axis_sum_allreduce_kernel<0>;
+  int grid = 0;
+  const int64_t work = axis == 0 ? (n_out + kCollThreads / 32 - 1) / (kCollThreads / 32) : (n_out + 31) / 32;
+  int rc = coll_grid(k, work, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev, (void*)&nx, (void*)&ny, (void*)&ld, (void*)&axis, (void*)&n_out};
+  return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1, GMT_EINVAL, "gmt_barrier: bad argument");
+  void* args[] = {(void*)&ranks_dev};
+  return coll_launch((const void*)barrier_kernel, 1, n_ranks, args, as_stream(stream));
+}
+
+}  // extern "C"

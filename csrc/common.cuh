@@ -145,7 +145,7 @@ inline int sm_count()
 inline cudaStream_t as_stream(gmt_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 template <typename T>
-inline bool aligned(const T* p, size_t a)
+__host__ __device__ inline bool aligned(const T* p, size_t a)
 {
   return (reinterpret_cast<uintptr_t>(p) % a) == 0;
 }

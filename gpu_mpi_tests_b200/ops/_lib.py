@@ -74,8 +74,11 @@ class Halo2dRank(C.Structure):
 class CollRank(C.Structure):
     _fields_ = [
         ("rank", C.c_int32), ("world", C.c_int32),
-        ("peer_buf", c_ptr), ("peer_flag", c_ptr), ("mc_buf", c_ptr),
+        ("peer_buf", c_ptr), ("mc_buf", c_ptr),
+        ("peer_stage", c_ptr), ("mc_stage", c_ptr), ("stage_cap", c_i64),
+        ("peer_flag", c_ptr),
         ("epoch", c_ptr), ("done", c_ptr), ("status", c_ptr), ("scratch", c_ptr),
+        ("inp", c_ptr), ("out", c_ptr), ("y", c_ptr),   # `in` in the C struct
         ("spin_limit", c_i64),
     ]
 
@@ -127,11 +130,11 @@ _SIGS = {
     "gmt_fused_stencil1d_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_fused_stencil2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, C.c_int, c_ptr]),
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),
-    "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, c_ptr, C.c_int, c_ptr]),
+    "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_gather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
-    "gmt_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, c_ptr]),
-    "gmt_daxpy_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_dbl, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
-    "gmt_axis_sum_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, c_i64, c_ptr, C.c_int, c_i64, c_i64, c_ptr]),
+    "gmt_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
+    "gmt_daxpy_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_dbl, c_ptr]),
+    "gmt_axis_sum_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, c_i64, C.c_int, c_i64, c_ptr]),
     "gmt_barrier": (None, [c_ptr, C.c_int, c_ptr]),
 }
 

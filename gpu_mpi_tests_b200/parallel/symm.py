@@ -97,10 +97,6 @@ class TorchSymmSpace(PeerSpace):
         self.rt, self.world, self.device = rt, rt.world_size, rt.device
         self.ranks_here = [rt.rank]
         self.group = dist.group.WORLD
-        try:
-            symm_mem.enable_symm_mem_for_group(self.group.group_name)
-        except Exception:  # noqa: BLE001 - newer torch enables lazily
-            pass
 
     def alloc(self, nbytes: int) -> SymmBuffer:
         nbytes = _round_up(max(nbytes, ALIGN))

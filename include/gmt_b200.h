@@ -248,46 +248,59 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
 /* flag words needed on `side` for the given interior extents */
 int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
 
-/* Collectives written as kernels over peer memory.  `bufs_dev`/`flags_dev` are device
- * arrays of world pointers (one per rank, index = rank), all ranks call with the same
- * epoch sequence.  A rank-local state block carries the epoch.                 */
+/* ================================================================ collectives
+ * written as kernels over peer memory: no MPI, no NCCL.  Like the fused stencils they take a
+ * DEVICE array of per-rank descriptors (blockIdx.y selects one): one entry per process in
+ * production, all ranks in one cooperative launch when emulated on a single GPU.
+ *
+ * Signalling: every rank owns a flag block of GMT_COLL_FLAG_WORDS words; word [round*32 + src]
+ * holds the last epoch rank `src` signalled for that round (st.release.sys / ld.acquire.sys,
+ * bounded spins).  Epochs only grow; reduction inputs travel through a staging area that is
+ * double-buffered by epoch parity, so a rank that is one call ahead cannot disturb a slower one. */
+#define GMT_COLL_FLAG_WORDS 64
+#define GMT_COLL_MAX_WORLD 32
 typedef struct {
   int32_t rank, world;
-  double** peer_buf;       /* device array [world]: peer-mapped base of each rank's buffer */
-  uint64_t** peer_flag;    /* device array [world]: peer-mapped flag block of each rank (>= world*8 words) */
-  double* mc_buf;          /* multicast VA of the buffer, or NULL */
-  uint64_t* epoch;         /* device-resident epoch counter (this rank) */
-  uint32_t* done;
-  uint32_t* status;
-  void* scratch;           /* local reduce scratch (gmt_reduce_scratch_bytes) */
+  double** peer_buf;      /* device array [world]: each rank's symmetric USER buffer (allgather/gather) */
+  double* mc_buf;         /* NVLS multicast address of that buffer, or NULL */
+  double** peer_stage;    /* device array [world]: each rank's staging area, 4*stage_cap doubles:
+                             inputs [parity][stage_cap] then results [parity][stage_cap] */
+  double* mc_stage;       /* multicast address of the staging area, or NULL */
+  int64_t stage_cap;
+  uint64_t** peer_flag;   /* device array [world]: each rank's flag block */
+  uint64_t* epoch;        /* device-resident epoch counter of this rank */
+  uint32_t* done;         /* >= 4 zero-initialised words (self-resetting) */
+  uint32_t* status;       /* non-zero when a bounded spin expired */
+  void* scratch;          /* gmt_reduce_scratch_bytes() of zeroed local scratch */
+  const double* in;       /* local operand: allgather source / all-reduce input / axis-sum array / daxpy x */
+  double* out;            /* local result: all-reduce output vector / global sum */
+  double* y;              /* daxpy y */
   int64_t spin_limit;
 } gmt_coll_rank;
 
-/* in-place allgather: rank r's slice [r*n,(r+1)*n) of its own buffer is stored into the same
- * offset of every peer's buffer (MPI_Allgather(MPI_IN_PLACE), mpi_daxpy_nvtx.cc:285,
- * mpigatherinplace.f90:39).  src == NULL means in place; otherwise the slice is read from
- * src (mpi_daxpy_nvtx.cc:288).  use_multicast: store through mc_buf (multimem.st).   */
-int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, const double* const* src_dev,
+/* in-place allgather: rank r's slice [r*n,(r+1)*n) is stored into the same offset of every
+ * peer's buffer (MPI_Allgather(MPI_IN_PLACE), mpi_daxpy_nvtx.cc:285, mpigatherinplace.f90:39).
+ * from_in != 0: the slice is read from `in` instead of the rank's own slot, and also stored
+ * locally (MPI_Allgather with a separate send buffer, mpi_daxpy_nvtx.cc:288).
+ * use_multicast != 0: one multimem.st per 16 bytes through mc_buf instead of world-1 stores. */
+int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int from_in,
                       int use_multicast, gmt_stream_t stream);
-/* gather to root in place (MPI_Gather(MPI_IN_PLACE), BASELINE config 5) */
-int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int root,
-                   gmt_stream_t stream);
-/* in-place sum all-reduce of a vector of n doubles living at offset `off` of every rank's
- * buffer (MPI_Allreduce(MPI_IN_PLACE), mpi_stencil2d_gt.cc:615,624).
- * algo: 0 = one-shot P2P read, 1 = two-shot P2P, 2 = multimem.ld_reduce one-shot     */
-int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int64_t off, int algo,
-                      gmt_stream_t stream);
-/* fused daxpy + global sum: y <- a x + y on each rank, every rank's out_sum <- sum over all
- * ranks of sum(y)  (mpi_daxpy_nvtx.cc:245-310 collapsed).  The rank partial goes through slot
- * `off` (doubles) of the symmetric buffer: [off + r] for r < world.               */
+/* gather to root in place (MPI_Gather with MPI_IN_PLACE at the root, BASELINE config 5) */
+int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int root, gmt_stream_t stream);
+/* sum all-reduce of n doubles: out <- sum over ranks of in; out may alias in
+ * (MPI_Allreduce(MPI_IN_PLACE), mpi_stencil2d_gt.cc:615,624).  n <= stage_cap.
+ * algo: 0 one-shot (every rank reads every peer's vector), 1 two-shot (reduce-scatter then
+ * allgather by peer stores), 2 one-shot through NVLS multimem.ld_reduce (needs mc_stage).
+ * Ranks add in rank order, so every rank gets the same bits (algos 0 and 1).            */
+int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int algo, gmt_stream_t stream);
+/* fused daxpy + global sum: y <- a*in + y on each rank, every rank's *out <- sum over all ranks
+ * of sum(y_new)  (cublasDaxpy + MPI_Allgather + host sums, mpi_daxpy_nvtx.cc:245-310, in one kernel) */
 int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, double a,
-                            const double* const* x_dev, double* const* y_dev, double* const* out_dev,
-                            int64_t off, gmt_stream_t stream);
-/* axis sum whose epilogue all-reduces the n_out-vector in place at `off` of the symmetric
- * buffer (gt::sum_axis_to + MPI_Allreduce, mpi_stencil2d_gt.cc:611-625)              */
+                            gmt_stream_t stream);
+/* axis sum of the column-major (nx, ny, ld) array `in` whose epilogue all-reduces the first n_out
+ * entries across ranks into `out` (gt::sum_axis_to + MPI_Allreduce, mpi_stencil2d_gt.cc:611-625) */
 int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
-                               int64_t ld, const double* const* z_dev, int axis, int64_t n_out,
-                               int64_t off, gmt_stream_t stream);
+                               int64_t ld, int axis, int64_t n_out, gmt_stream_t stream);
 /* signal barrier across ranks (MPI_Barrier, mpi_daxpy_nvtx.cc:277) */
 int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream);
 

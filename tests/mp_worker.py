@@ -74,7 +74,66 @@ def case_baseline(rt, args):
         print("baseline ok", flush=True)
 
 
-CASES = {"fused": case_fused, "baseline": case_baseline}
+def case_collectives(rt, args):
+    """The in-kernel collectives across real GPUs (P2P and, when available, NVLS multicast)."""
+    from gpu_mpi_tests_b200.parallel.collectives import PeerCollectives
+    from gpu_mpi_tests_b200.parallel.symm import make_space
+    from gpu_mpi_tests_b200.utils import oracle
+    space = make_space(rt)
+    W, r, dev = rt.world_size, rt.rank, rt.device
+    n = 1 << 18
+    pc = PeerCollectives(space, buf_doubles=W * n, stage_cap=1 << 16, spin_limit=1 << 26)
+    variants = [False] + ([True] if pc.has_multicast else [])
+    for mc in variants:
+        for it in range(3):
+            b = pc.buffer(r)
+            b.fill_(-1.0)
+            b[r * n:(r + 1) * n] = oracle.gather_slot_values(r + 1, n, dev) + it
+            pc.allgather_inplace(n, multicast=mc)
+            torch.cuda.synchronize()
+            for p in range(W):
+                ref = oracle.gather_slot_values(p + 1, n, dev) + it
+                assert torch.equal(b[p * n:(p + 1) * n], ref), f"allgather mc={mc} it={it} slot {p}"
+            rt.barrier()
+    b = pc.buffer(r)
+    b.fill_(-1.0)
+    b[r * n:(r + 1) * n] = float(r + 1)
+    pc.gather_inplace(n, 0)
+    torch.cuda.synchronize()
+    rt.barrier()
+    if r == 0:
+        for p in range(W):
+            assert float(b[p * n]) == p + 1 and float(b[(p + 1) * n - 1]) == p + 1
+    algos = ["one_shot", "two_shot"] + (["multimem"] if pc.has_multicast else [])
+    for algo in algos:
+        for m in (1, 1024, 1 << 16):
+            for it in range(3):
+                v = torch.full((m,), float(r + 1 + it), dtype=torch.float64, device=dev)
+                pc.allreduce({r: v}, algo=algo)
+                torch.cuda.synchronize()
+                expect = sum(p + 1 + it for p in range(W))
+                assert float((v - expect).abs().max()) < 1e-12, f"allreduce {algo} m={m}"
+    x, y = oracle.daxpy_init_scaled(1 << 20, dev)
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    pc.daxpy_allreduce(2.0, {r: x}, {r: y}, {r: out})
+    torch.cuda.synchronize()
+    expect = oracle.daxpy_scaled_expected_allsum(1 << 20, W)
+    assert abs(out.item() - expect) < 1e-6 * expect, (out.item(), expect)
+    z = torch.full((64, 128), float(r + 1), dtype=torch.float64, device=dev)
+    o = torch.zeros(64, dtype=torch.float64, device=dev)
+    pc.axis_sum_allreduce({r: z}, 0, {r: o})
+    torch.cuda.synchronize()
+    assert float((o - 128 * sum(p + 1 for p in range(W))).abs().max()) < 1e-9
+    for _ in range(10):
+        pc.barrier()
+    torch.cuda.synchronize()
+    pc.check_status()
+    rt.barrier()
+    if r == 0:
+        print("collectives ok (multicast: %s)" % pc.has_multicast, flush=True)
+
+
+CASES = {"fused": case_fused, "baseline": case_baseline, "collectives": case_collectives}
 
 if __name__ == "__main__":
     name = sys.argv[1]

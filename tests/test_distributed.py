@@ -46,3 +46,12 @@ def test_baseline_exchange_nccl():
         pytest.skip("needs >= 2 GPUs")
     out = run_workers(2, "baseline")
     assert "baseline ok" in out
+
+
+@pytest.mark.gpu
+def test_collectives_across_gpus():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    out = run_workers(n if n in (2, 4, 8) else 2, "collectives")
+    assert "collectives ok" in out
