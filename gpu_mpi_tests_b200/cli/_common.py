@@ -1,0 +1,56 @@
+"""Shared plumbing of the CLI programs: runtime start-up, fail-fast exits with the reference's
+messages and exit codes, flag parsing that leaves the positional arguments untouched."""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+from ..parallel import decomp, runtime
+from ..utils import report
+
+
+def base_parser(description: str) -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(description=description)
+    ap.add_argument("--impl", choices=["fused", "baseline"], default=None,
+                    help="peer-memory kernels or the library-only restatement (default: fused on GPUs)")
+    ap.add_argument("--cpu", action="store_true", help="force the CPU/gloo flavour")
+    return ap
+
+
+def start(args) -> tuple:
+    """MPI_Init + set_rank_device: returns (rt, out, impl).  A bad rank/device ratio prints the
+    reference's message and exits 1 (mpi_daxpy.cc:43-47)."""
+    if getattr(args, "cpu", False):
+        os.environ["GMT_FORCE_CPU"] = "1"
+    out = report.Printer()
+    try:
+        rt = runtime.init()
+    except runtime.RankDeviceError as e:
+        out(str(e))
+        sys.exit(1)
+    impl = args.impl or ("fused" if rt.is_cuda else "baseline")
+    if impl == "fused" and not rt.is_cuda:
+        out("fused kernels need a CUDA device; using the baseline (library-only) path")
+        impl = "baseline"
+    return rt, out, impl
+
+
+def finish(rt) -> None:
+    sys.stdout.flush()
+    runtime.finalize()
+
+
+def slab_or_exit(n_global: int, rt, out) -> decomp.Slab1D:
+    """Divisibility check with the reference's message and exit(1) (mpi_stencil_gt.cc:141-145)."""
+    try:
+        return decomp.Slab1D(n_global, rt.world_size, rt.rank)
+    except decomp.DecompositionError as e:
+        out(str(e))
+        sys.exit(1)
+
+
+def getenv_memory_per_core(rt, out) -> None:
+    """Rank 0 echoes MEMORY_PER_CORE (mpi_daxpy.cc:101-108)."""
+    if rt.rank == 0:
+        out(report.memory_per_core(os.environ.get("MEMORY_PER_CORE")))

@@ -1,0 +1,98 @@
+"""mpi_stencil2d_sycl (mpi_stencil2d_sycl.cc:377-556): the dim-0 case of the 2-D test without
+the array library.  argv: [nx_local=1024] [stage_host: first char '1'] [n_iter=100]; warm-up 5,
+ny = 512*1024.  Prints a device line per rank, the parameter block, the device-bytes estimate,
+per rank `exchange time <ms per iteration>` and `err_norm`."""
+from __future__ import annotations
+
+import sys
+import time
+
+import torch
+
+from ..models.stencil2d import Stencil2DWorkload
+from ..ops import local
+from ..parallel.symm import make_space
+from ..utils import report
+from . import _common
+
+
+def device_line(rt) -> str:
+    if rt.props is not None:
+        p = rt.props
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain, p.pci_bus, p.pci_device)
+        uuid = "".join("%02x" % b for b in bytes(p.uuid)[:8])
+    else:
+        bdf, uuid = "cpu", "0" * 16
+    return report.sycl_device_line(rt.rank, bdf, uuid)
+
+
+def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_style: str):
+    space = make_space(rt) if impl == "fused" else None
+    r, W = rt.rank, rt.world_size
+    if impl == "baseline":
+        wl = Stencil2DWorkload(rt, nx_local, ny, mode="dim0", impl="baseline",
+                               stage="host" if stage_host else "device")
+    else:
+        wl = Stencil2DWorkload(rt, nx_local, ny, mode="dim0", impl="fused", with_err=False, space=space)
+    wl.setup()
+    total = 0.0
+    if impl == "baseline":
+        for i in range(n_warmup + n_iter):
+            t0 = time.perf_counter()
+            wl.plan.exchange()
+            dt = time.perf_counter() - t0
+            if i >= n_warmup:
+                total += dt
+            wl.plan.stencil()
+            if rt.is_cuda:
+                torch.cuda.synchronize()
+    else:
+        for _ in range(n_warmup):
+            wl.step()
+        torch.cuda.synchronize()
+        rt.barrier()
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        for _ in range(n_iter):
+            wl.step()
+        e1.record()
+        for _ in range(n_iter):
+            local.stencil2d(wl.z[r], 0, wl.sx, out=wl.out[r])
+        e2.record()
+        torch.cuda.synchronize()
+        total = max(0.0, (e0.elapsed_time(e1) - e1.elapsed_time(e2)) * 1e-3)
+        wl.step()
+    ms = total / max(n_iter, 1) * 1000
+    err = wl.err_norm(r)
+    wl.check()
+    if line_style == "sycl":
+        out(report.exchange_time_ms(r, W, ms))
+        out(report.err_norm_line(r, W, rt.device_id, rt.vendor_id, err))
+    else:
+        out(report.oo_exchange_time(r, ms))
+        out(report.oo_err_norm(r, rt.vendor_id, err))
+
+
+def main(argv=None) -> int:
+    ap = _common.base_parser(__doc__)
+    ap.add_argument("nx_local", nargs="?", type=int, default=1024)
+    ap.add_argument("stage_host", nargs="?", default="0")
+    ap.add_argument("n_iter", nargs="?", type=int, default=100)
+    ap.add_argument("--ny", type=int, default=512 * 1024)
+    args = ap.parse_args(argv)
+    rt, out, impl = _common.start(args)
+    stage_host = args.stage_host[:1] == "1"
+    n_warmup = 5
+    W = rt.world_size
+    out(device_line(rt))
+    if rt.rank == 0:
+        out(report.sycl_banner(W, rt.rank, args.ny, args.nx_local * W, args.nx_local, args.n_iter, n_warmup, stage_host))
+        nbytes = 8.0 * ((args.nx_local + 4) * args.ny + args.nx_local * args.ny + 4 * 2 * args.ny)
+        out(report.dev_bytes(nbytes))
+    run_dim0(rt, out, impl, args.nx_local, args.ny, args.n_iter, n_warmup, stage_host, "sycl")
+    _common.finish(rt)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

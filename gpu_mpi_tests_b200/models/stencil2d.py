@@ -55,7 +55,7 @@ class Stencil2DWorkload:
                 raise RuntimeError("impl='fused' needs CUDA; use impl='baseline' on the CPU/gloo path")
             self.space = space if space is not None else make_space(self.rt)
             self.plan = FusedStencil2D(self.space, self.px, self.py, nx, ny, self.gx, self.gy, with_err=with_err,
-                                       spin_limit=spin_limit)
+                                       spin_limit=spin_limit, mem_space=mem_space)
             self.ranks = self.plan.ranks
             self.z, self.out = self.plan.z, self.plan.out
             self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy

@@ -135,7 +135,7 @@ class FusedStencil2D(_PlanBase):
 
     def __init__(self, space: PeerSpace, px: int, py: int, nx: int, ny: int, gx: int = 2, gy: int = 2,
                  with_err: bool = True, spin_limit: int = 0, dx: float | None = None, dy: float | None = None,
-                 wx: float = 1.0, wy: float = 1.0):
+                 wx: float = 1.0, wy: float = 1.0, mem_space: str = "device"):
         super().__init__(space, with_err, spin_limit)
         if px * py != space.world:
             raise ValueError(f"grid {px}x{py} does not match world {space.world}")
@@ -148,8 +148,11 @@ class FusedStencil2D(_PlanBase):
         self.sy = wy / self.dy if gy else 0.0
         self.grids = {r: Grid2D(px, py, r) for r in self.ranks}
         self.ldz = nx + 2 * gx
-        self.z = {r: torch.empty(ny + 2 * gy, self.ldz, dtype=F64, device=self.device) for r in self.ranks}
-        self.out = {r: torch.empty(ny, nx, dtype=F64, device=self.device) for r in self.ranks}
+        # only inboxes and flags are touched by peers; the arrays themselves may live in any
+        # memory space the GPU can address (device, or managed for the TEST_MANAGED flavours)
+        from . import array as ga
+        self.z = {r: ga.empty((ny + 2 * gy, self.ldz), mem_space, self.device) for r in self.ranks}
+        self.out = {r: ga.empty((ny, nx), mem_space, self.device) for r in self.ranks}
         nfx = int(lib.gmt_halo2d_flag_count(0, nx, ny))
         nfy = int(lib.gmt_halo2d_flag_count(2, nx, ny))
         box_x, box_y = 2 * ny * 8, 2 * nx * 8

@@ -255,7 +255,9 @@ class Printer:
         for ln in ([line] if isinstance(line, str) else line):
             if self.lines is not None:
                 self.lines.append(ln)
-            print(ln, file=self.stream, flush=True)
+            # one write per line: ranks share the terminal and must not interleave mid-line
+            self.stream.write(ln + "\n")
+            self.stream.flush()
 
 
 class JsonlSink:

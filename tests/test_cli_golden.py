@@ -1,0 +1,179 @@
+"""Golden-output tests: run each CLI program (CPU/gloo flavour here; the GPU flavour is run
+by test_cli_gpu below) and match the exact line formats of the reference."""
+import os
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+_port = [29800 + (os.getpid() % 150)]
+
+
+def run_cli(module, *args, nproc=1, env_extra=None, cpu=True, timeout=600, expect_rc=0):
+    env = dict(os.environ)
+    if cpu:
+        env["GMT_FORCE_CPU"] = "1"
+    env.update(env_extra or {})
+    if nproc == 1:
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+            env.pop(k, None)
+        cmd = [sys.executable, "-m", f"gpu_mpi_tests_b200.cli.{module}", *map(str, args)]
+    else:
+        _port[0] += 1
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+               "--master-addr", "127.0.0.1", "--master-port", str(_port[0]), "-m",
+               f"gpu_mpi_tests_b200.cli.{module}", *map(str, args)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
+    assert res.returncode == expect_rc, f"{module}: rc={res.returncode}\n{res.stdout[-2000:]}\n{res.stderr[-3000:]}"
+    return [ln for ln in res.stdout.splitlines() if ln.strip()]
+
+
+def match_all(lines, patterns):
+    """Every pattern matches at least one line, in order of first appearance not required."""
+    for pat in patterns:
+        assert any(re.fullmatch(pat, ln) for ln in lines), f"no line matches {pat!r} in\n" + "\n".join(lines)
+
+
+F = r"-?\d+\.\d{6}"
+F8 = r"\d+\.\d{8}"
+
+
+def test_daxpy_prints_every_element_and_sum():
+    lines = run_cli("daxpy")
+    assert len(lines) == 1025
+    assert lines[0] == "1.000000" and lines[1023] == "1024.000000"
+    assert lines[-1] == "SUM = 524800.000000"
+    assert run_cli("daxpy_nvtx", "--quiet") == ["SUM = 524800.000000"]
+
+
+def test_mpi_daxpy_and_gt_world2():
+    lines = run_cli("mpi_daxpy", nproc=2)
+    match_all(lines, [r"MEMORY_PER_CORE is not set", r"RANK\[1/2\] => DEVICE\[1/2\] mem=\d+",
+                      r"RANK\[2/2\] => DEVICE\[2/2\] mem=\d+", r"CUDA PreferredLocation of 'm_y' is .+",
+                      r"0/2 SUM = 524800\.000000", r"1/2 SUM = 524800\.000000"])
+    lines = run_cli("mpi_daxpy_gt", nproc=2)
+    match_all(lines, [r"0/2 \[0:0x[0-9a-f]{8}\] SUM = 524800\.000000", r"1/2 \[1:0x[0-9a-f]{8}\] SUM = 524800\.000000"])
+
+
+def test_mpi_daxpy_nvtx_world2_closed_forms():
+    """BASELINE config 1: fp64 daxpy + global sum, n = 2^20 per rank, world_size = 2, gloo."""
+    lines = run_cli("mpi_daxpy_nvtx", "--n-per-node", 2 * (1 << 20), "--barrier", nproc=2,
+                    env_extra={"MEMORY_PER_CORE": "2048"})
+    match_all(lines, [r"1 nodes, 2 ranks, 1048576 elements each, total 2097152", r"MEMORY_PER_CORE=2048",
+                      r"GPU memory \d+\.\d{3} / \d+\.\d{3} \(\d+\.\d{3}\) MB",
+                      r"0/2 SUM = 524288\.500000", r"1/2 SUM = 524288\.500000",
+                      r"0/2 ALLSUM = 1048577\.000000", r"1/2 ALLSUM = 1048577\.000000",
+                      r"0/2 TIME total  : \d+\.\d{3}", r"1/2 TIME kernel : \d+\.\d{3}",
+                      r"0/2 TIME barrier: \d+\.\d{3}", r"1/2 TIME gather : \d+\.\d{3}"])
+
+
+def test_mpienv():
+    lines = run_cli("mpienv", nproc=2, env_extra={"MEMORY_PER_CORE": "4096"})
+    match_all(lines, [r" rank\s+0\s+MEMORY_PER_CORE=\s+4096", r" rank\s+1\s+MEMORY_PER_CORE=\s+4096"])
+
+
+def test_mpigatherinplace_world4():
+    lines = run_cli("mpigatherinplace", 1000, nproc=4)
+    from gpu_mpi_tests_b200.utils import oracle
+    asum = oracle.gather_all_sum(4, 1000)
+    for r in range(4):
+        want = r"\s+%d /\s+4\s+%s\s+%s" % (r, re.escape("%.8E" % oracle.gather_slot_sum(r, 1000)), re.escape("%.8E" % asum))
+        match_all(lines, [want])
+
+
+def test_mpi_stencil_gt_world2_and_divisor_error():
+    lines = run_cli("mpi_stencil_gt", 1, nproc=2)
+    match_all(lines, [r"n procs  = 2", r"n_global = 1048576", r"n_local  = 524288",
+                      rf"0/2 exchange time {F8}", rf"1/2 exchange time {F8}",
+                      rf"0/2 \[0:0x[0-9a-f]{{8}}\] err_norm = {F8}", rf"1/2 \[1:0x[0-9a-f]{{8}}\] err_norm = {F8}"])
+    for ln in lines:
+        m = re.search(r"err_norm = (\S+)", ln)
+        if m:
+            assert float(m.group(1)) < 1e-3  # a stale ghost would give > 1e4
+    lines = run_cli("mpi_stencil_gt", "--points", 1000, nproc=3, expect_rc=1)
+    match_all(lines, [r"\d nmpi \(3\) must be divisor of domain size \(1000\), exiting"])
+
+
+def test_mpi_stencil2d_gt_twelve_lines_world2():
+    lines = run_cli("mpi_stencil2d_gt", 32, 3, "--n-other", 64, nproc=2)
+    match_all(lines, [r"n procs        = 2", r"n_global_deriv = 64", r"n_global_other = 64", r"n_iter         = 3",
+                      r"n_warmup       = 10"])
+    tests = [ln for ln in lines if ln.startswith("TEST")]
+    assert len(tests) == 12
+    order = [(d, s, b) for d in (0, 1) for s in ("device ", "managed") for b in (1, 0)]
+    for ln, (d, s, b) in zip(tests[:8], order):
+        m = re.fullmatch(rf"TEST dim:{d}, {s}, buf:{b}; ({F8}), err=({F8})", ln)
+        assert m, ln
+        assert float(m.group(2)) < 1e-6
+    for ln, (d, s) in zip(tests[8:], [(0, "device "), (0, "managed"), (1, "device "), (1, "managed")]):
+        assert re.fullmatch(rf"TEST dim:{d}, {s}, buf:0; allreduce={F8}", ln), ln
+
+
+def test_sycl_variants_world2():
+    lines = run_cli("mpi_stencil2d_sycl", 16, 1, 3, "--ny", 64, nproc=2)
+    match_all(lines, [r"0 \S+\([0-9a-f]+\)", r"n procs    = 2", r"nx_global  = 32", r"stage_host = 1", r"dev bytes  = \d+\.\d{3} (MB|GB)",
+                      rf"0/2 exchange time {F8} ms", rf"1/2 \[1:0x[0-9a-f]{{8}}\] err_norm = {F8}"])
+    lines = run_cli("mpi_stencil2d_sycl_oo", 1, 0, 2, nproc=2)
+    match_all(lines, [r"n_global   = 1024", r"n_local    = 512", rf"0: exchange time {F8} ms", rf"1: \[0x[0-9a-f]{{8}}\] err_norm = {F8}"])
+
+
+def test_rank_device_ratio_error_exit1():
+    lines = run_cli("mpi_daxpy", nproc=3, env_extra={"GMT_FAKE_DEVICES": "2"}, expect_rc=1)
+    match_all(lines, [r"ERROR: Number of ranks \(3\) not a multiple of number of GPUs \(2\)"])
+
+
+def test_oversubscription_two_ranks_per_device():
+    lines = run_cli("mpi_daxpy", nproc=4, env_extra={"GMT_FAKE_DEVICES": "2"})
+    match_all(lines, [r"RANK\[1/4\] => DEVICE\[1/2\] mem=\d+", r"RANK\[2/4\] => DEVICE\[1/2\] mem=\d+",
+                      r"RANK\[4/4\] => DEVICE\[2/2\] mem=\d+"])
+
+
+def test_avg_and_run_command(tmp_path):
+    from gpu_mpi_tests_b200.cli import avg, run
+    f = tmp_path / "out-noum_none_1_2.txt"
+    f.write_text("0/2 TIME gather : 0.500\n1/2 TIME gather : 0.250\n0/2 TIME kernel : 0.100\n")
+    mean, n = avg.average(str(f), "gather")
+    assert n == 2 and mean == pytest.approx(0.375)
+    assert avg.average(str(f), "kernel")[0] == pytest.approx(0.1)
+    cmd, outfile = run.build_command("um", "none", 1, 4, [])
+    assert outfile == "out-um_none_1_4.txt" and "--managed" in cmd and "--nproc-per-node=4" in cmd
+    cmd, _ = run.build_command("noum", "ncu", 1, 2, ["--barrier"])
+    assert cmd[0] == "ncu" and "--profile-from-start" in cmd and "--managed" not in cmd and cmd[-1] == "--barrier"
+
+
+def test_nvtx_ranges_of_daxpy_nvtx():
+    from gpu_mpi_tests_b200.utils import nvtx
+    nvtx.reset_trace()
+    with nvtx.profiler_window():
+        with nvtx.nvtx_range("mpiAllGather"):
+            with nvtx.nvtx_range("x"):
+                pass
+            with nvtx.nvtx_range("y"):
+                pass
+    ev = nvtx.trace()
+    assert ev[0][0] == "profiler_start" and ev[-1][0] == "profiler_stop"
+    assert [(k, d, n) for (k, d, n) in ev if k == "push"] == [("push", 0, "mpiAllGather"), ("push", 1, "x"), ("push", 1, "y")]
+
+
+@pytest.mark.gpu
+def test_cli_gpu_fused_single_rank():
+    """The GPU flavour of the programs on one B200 (fused kernels, world of one)."""
+    lines = run_cli("mpi_stencil_gt", 4, cpu=False)
+    match_all(lines, [r"n_global = 4194304", rf"0/1 exchange time {F8}", rf"0/1 \[0:0x[0-9a-f]{{8}}\] err_norm = {F8}"])
+    lines = run_cli("mpi_stencil2d_gt", 64, 5, "--n-other", 4096, cpu=False)
+    tests = [ln for ln in lines if ln.startswith("TEST")]
+    assert len(tests) == 12
+    for ln in tests[:8]:
+        assert float(re.search(r"err=(\S+)", ln).group(1)) < 1e-6
+    lines = run_cli("mpi_daxpy_nvtx", "--n-per-node", 1 << 20, "--managed", cpu=False)
+    match_all(lines, [r"0/1 SUM = 524288\.500000", r"0/1 ALLSUM = 524288\.500000",
+                      r"CUDA PreferredLocation of 'd_x' is (CPU|DEVICE|INVALID) \(-?\d+\)"])
+    lines = run_cli("mpi_daxpy", cpu=False)
+    match_all(lines, [r"CUDA PreferredLocation of 'd_x' is UNMANAGED", r"CUDA PreferredLocation of 'x' is NOT CUDA",
+                      r"CUDA PreferredLocation of 'm_x' is .+", r"0/1 SUM = 524800\.000000"])
+    lines = run_cli("mpigatherinplace", 1 << 20, cpu=False)
+    assert len(lines) == 1
