@@ -9,9 +9,10 @@
 // The reference packs strips into staging buffers, hands them to MPI, waits, unpacks, and
 // brackets all of it with device-wide syncs before the stencil may start.  Here one
 // persistent kernel per rank does everything:
-//   phase 1  every CTA stores its share of this rank's boundary values straight into the
-//            neighbours' inboxes (ordinary stores on NVLink-mapped addresses), one
-//            system-scope fence per CTA, then one st.release.sys flag per chunk;
+//   phase 1  a few CTAs store this rank's boundary values straight into the neighbours'
+//            inboxes (ordinary stores on NVLink-mapped addresses), chunk by chunk in the order
+//            the neighbour will need them, each chunk followed by a system-scope fence and a
+//            st.release.sys flag; all other CTAs start computing immediately;
 //   phase 2  CTAs draw tiles from an atomic counter: interior tiles first (they depend on
 //            nobody), boundary tiles last; a boundary tile polls its chunk flags
 //            (ld.acquire.sys, bounded), copies the inbox into the array's own ghost cells
@@ -184,58 +185,63 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
 
   // ---------------- phase 1: export boundary chunks.  x faces: kFlagCols columns x 2 rows
   // (strided 16-byte pieces gathered into a contiguous inbox); y faces: kTileI rows x 2 columns.
+  // Only the first kPushCtas CTAs export (then join the tile loop late); everybody else starts
+  // computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
+  // each followed by its own fence + flag, so the exchange streams underneath the sweep: the
+  // export front moves ~10x faster than the compute front and only the very first chunk's
+  // latency can ever be exposed.
+  constexpr int kPushCtas = 32;
   const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
   const int64_t nfy = GY ? M.tiles_i : 0;
   const int64_t nunits = 2 * (nfx + nfy);
-  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-    int side;
-    int64_t c;
-    if (u < 2 * nfx) {
-      side = (int)(u / nfx);
-      c = u % nfx;
-    } else {
-      side = 2 + (int)((u - 2 * nfx) / nfy);
-      c = (u - 2 * nfx) % nfy;
-    }
-    if (!R.has[side]) continue;
-    double* box = R.peer_inbox[side][par];
-    if (side < 2) {
-      const int64_t j0 = c * kFlagCols;
-      const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
-      double2 v[kFlagCols / kStThreads];
-#pragma unroll
-      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-        const int64_t j = j0 + tid + q * kStThreads;
-        if (j < ny) v[q] = ldg128(src + j * ldz);
+  const int npush = min((int)gridDim.x, kPushCtas);
+  if ((int)blockIdx.x < npush) {
+    for (int64_t u = blockIdx.x; u < nunits; u += npush) {
+      int side;
+      int64_t c;
+      if (u < 2 * nfx) {
+        side = (int)(u & 1);
+        c = u >> 1;
+      } else {
+        side = 2 + (int)((u - 2 * nfx) & 1);
+        c = (u - 2 * nfx) >> 1;
       }
+      if (!R.has[side]) continue;  // CTA-uniform
+      double* box = R.peer_inbox[side][par];
+      if (side < 2) {
+        const int64_t j0 = c * kFlagCols;
+        const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
+        double2 v[kFlagCols / kStThreads];
 #pragma unroll
-      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-        const int64_t j = j0 + tid + q * kStThreads;
-        if (j < ny) stg128(box + 2 * j, v[q]);
-      }
-    } else {
-      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
-      const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
-      double2 v[4];
+        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+          const int64_t j = j0 + tid + q * kStThreads;
+          if (j < ny) v[q] = ldg128(src + j * ldz);
+        }
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
-        if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
-      }
+        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+          const int64_t j = j0 + tid + q * kStThreads;
+          if (j < ny) stg128(box + 2 * j, v[q]);
+        }
+      } else {
+        const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+        const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
+        double2 v[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
-        if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
+        for (int q = 0; q < 4; ++q) {
+          const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+          if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+          if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
+        }
       }
-    }
-  }
-  __syncthreads();
-  if (tid == 0 && blockIdx.x < nunits) {
-    fence_sys();
-    for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-      const int side = u < 2 * nfx ? (int)(u / nfx) : 2 + (int)((u - 2 * nfx) / nfy);
-      const int64_t c = u < 2 * nfx ? u % nfx : (u - 2 * nfx) % nfy;
-      if (R.has[side]) st_release_sys(R.peer_flag[side] + c, e);
+      __syncthreads();
+      if (tid == 0) {
+        fence_sys();
+        st_release_sys(R.peer_flag[side] + c, e);
+      }
     }
   }
 

@@ -70,8 +70,6 @@ class Stencil2DWorkload:
         else:
             raise ValueError("impl must be fused or baseline")
         self._host_bc = None
-        self._err_host = None
-        self._dev_bc = None
 
     # ------------------------------------------------------------------ setup / step
     def setup(self, poison: float = 0.0) -> None:
@@ -89,10 +87,12 @@ class Stencil2DWorkload:
 
     # ------------------------------------------------------------------ end to end
     def _prepare_e2e(self) -> None:
-        """Pinned host copies of this rank's physical-boundary ghost values (the per-step input)
-        and a pinned scalar for the per-step result."""
-        self._host_bc, self._dev_bc = {}, {}
+        """Per-step host input and output: ONE pinned buffer holding this rank's physical-boundary
+        ghost values (all sides back to back), its device staging twin, and a pinned scalar for the
+        per-step result."""
         pin = self.device.type == "cuda"
+        self._bc_views = {}
+        total = 0
         for r in self.ranks:
             g = decomp.Grid2D(self.px, self.py, r)
             z = self.z[r]
@@ -107,43 +107,65 @@ class Stencil2DWorkload:
             if gy and g.neighbour(3) < 0:
                 views[3] = z[gy + ny:gy + ny + 2, gx:gx + nx]
             for side, v in views.items():
-                h = torch.empty(v.shape, dtype=F64, pin_memory=pin)
-                h.copy_(v)
-                self._host_bc[(r, side)] = (h, v)
-                if side < 2 and self.device.type == "cuda":
-                    self._dev_bc[(r, side)] = torch.empty(v.shape, dtype=F64, device=self.device)
-        self._err_host = {r: torch.zeros(1, dtype=F64, pin_memory=pin) for r in self.ranks}
+                self._bc_views[(r, side)] = (total, v)
+                total += v.numel()
+        self._bc_total = total
+        self._host_bc = torch.empty(max(total, 1), dtype=F64, pin_memory=pin)
+        self._dev_bc = torch.empty(max(total, 1), dtype=F64, device=self.device)
+        for (r, side), (off, v) in self._bc_views.items():
+            self._host_bc[off:off + v.numel()].view(v.shape).copy_(v)
+        self._err_dev = torch.zeros(len(self.ranks), dtype=F64, device=self.device)
+        self._err_host = torch.zeros(len(self.ranks), dtype=F64, pin_memory=pin)
+        self._graph = None
+        self._graph_failed = False
 
     def e2e_bytes(self) -> tuple[int, int]:
         """(host->device, device->host) bytes per step, counted from the tensors copied."""
         if self._host_bc is None:
             self._prepare_e2e()
-        h2d = sum(h.numel() * 8 for (h, _v) in self._host_bc.values())
-        d2h = 8 * len(self.ranks)
-        return h2d, d2h
+        return self._bc_total * 8, self._err_host.numel() * 8
 
-    def step_e2e(self) -> float:
-        """Upload boundary values, run the step, read the error norm back.  Returns the largest
-        err_norm over the ranks hosted by this process (host float: synchronises)."""
+    def _e2e_body(self) -> None:
+        """Stream-ordered body of one end-to-end step (also what gets captured in a CUDA graph)."""
+        if self._bc_total:
+            self._dev_bc.copy_(self._host_bc, non_blocking=True)          # one H2D for all sides
+            for (r, side), (off, v) in self._bc_views.items():
+                local.copy2d(self._dev_bc[off:off + v.numel()].view(v.shape), v)  # scatter into the ghosts
+        self.step()
+        for k, r in enumerate(self.ranks):
+            self._err_dev[k:k + 1].copy_(self.err_sumsq(r))
+        self._err_host.copy_(self._err_dev, non_blocking=True)             # one D2H
+
+    def step_e2e(self, use_graph: bool = True) -> float:
+        """What a time-stepping user calls: upload this step's boundary values from pinned host
+        memory, run the fused step, read the error norm back.  Returns the largest err_norm over
+        the ranks hosted by this process (host float: synchronises every call).  The stream work
+        of a step is captured once in a CUDA graph (a single-rank plan launches no cooperative
+        kernel, so it is capturable) and replayed: one launch per step instead of seven."""
         if self._host_bc is None:
             self._prepare_e2e()
-        for (r, side), (h, v) in self._host_bc.items():
-            if side < 2 and (r, side) in self._dev_bc:
-                # strided 2-wide strip: contiguous H2D into staging, then the unpack kernel
-                d = self._dev_bc[(r, side)]
-                d.copy_(h, non_blocking=True)
-                local.copy2d(d, v)
-            else:
-                v.copy_(h, non_blocking=True)
-        self.step()
-        worst = 0.0
-        for r in self.ranks:
-            self._err_host[r].copy_(self.err_sumsq(r), non_blocking=True)
-        if self.device.type == "cuda":
+        cuda = self.device.type == "cuda"
+        graphable = (use_graph and cuda and self.impl == "fused" and len(self.ranks) == 1
+                     and not self._graph_failed)
+        if graphable and self._graph is None:
+            try:
+                self._e2e_body()                      # warm-up outside capture
+                torch.cuda.synchronize(self.device)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._e2e_body()
+                self._graph = g
+            except Exception:  # noqa: BLE001 - capture is an optimisation, never a requirement
+                self._graph_failed = True
+                self._graph = None
+                torch.cuda.synchronize(self.device)
+        if graphable and self._graph is not None:
+            self._graph.replay()
+        else:
+            self._e2e_body()
+        if cuda:
             torch.cuda.current_stream().synchronize()
-        for r in self.ranks:
-            worst = max(worst, float(self._err_host[r].item()) ** 0.5)
-        return worst
+        return float(self._err_host.max().item()) ** 0.5
 
     # ------------------------------------------------------------------ validation
     def analytic(self, rank: int) -> torch.Tensor:
