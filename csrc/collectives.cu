@@ -79,15 +79,19 @@ __device__ __forceinline__ void wait_one(CollShared& S, int src, int round, uint
   __syncthreads();
 }
 
-// True in exactly one CTA of this rank: the last one to get here.  Everything the other CTAs
-// wrote before is visible (system scope) to whoever synchronises with that CTA afterwards.
-__device__ __forceinline__ bool arrive_last(CollShared& S, uint32_t* counter)
+// True in exactly one CTA of this rank: the last one to get here.  With publish = true,
+// everything the other CTAs wrote before is visible (system scope) to whoever synchronises
+// with that CTA afterwards (fence / relaxed atomic / fence); publish = false only counts.
+// A single-CTA grid needs neither the atomic nor the fences: the CTA barrier orders its own
+// writes before the release stores that follow.
+__device__ __forceinline__ bool arrive_last(CollShared& S, uint32_t* counter, bool publish = true)
 {
   __syncthreads();
+  if (gridDim.x == 1) return true;
   if (threadIdx.x == 0) {
-    fence_sys();
+    if (publish) fence_sys();
     S.last = (atomicAdd(counter, 1u) == gridDim.x - 1);
-    if (S.last) fence_sys();
+    if (S.last && publish) fence_sys();
   }
   __syncthreads();
   return S.last;
@@ -235,7 +239,7 @@ __device__ __forceinline__ void reduce_tail(CollShared& S, uint64_t e, int64_t n
     const double* res = S.stage[r] + res_off;
     for (int64_t i = t0; i < n; i += stride) out[i] = ld_peer_f64(res + i);
   }
-  if (arrive_last(S, S.R.done + 2)) coll_finish(S, e);
+  if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
 }
 
 template <int kAlgo>

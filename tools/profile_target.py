@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""Short single-GPU program for ncu: a few launches of each hot kernel at the BASELINE shapes.
+    python tools/profile_target.py [grid|dim0|dim1|1d|daxpy|all]"""
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch
+
+from gpu_mpi_tests_b200.ops import local
+from gpu_mpi_tests_b200.parallel.halo import FusedStencil1D, FusedStencil2D
+from gpu_mpi_tests_b200.parallel.symm import VirtualSpace
+
+what = sys.argv[1] if len(sys.argv) > 1 else "all"
+dev = torch.device("cuda", 0)
+torch.cuda.set_device(dev)
+space = VirtualSpace(1, dev)
+N = 3
+if what in ("grid", "all"):
+    p = FusedStencil2D(space, 1, 1, 16384, 16384, 2, 2, with_err=True)
+    p.init_analytic()
+    for _ in range(N):
+        p.step()
+    torch.cuda.synchronize()
+    print("grid err", p.err_norm(0))
+    del p
+if what in ("dim0", "all"):
+    p = FusedStencil2D(space, 1, 1, 1024, 524288, 2, 0, with_err=False)
+    p.init_analytic()
+    for _ in range(N):
+        p.step()
+    torch.cuda.synchronize()
+    del p
+if what in ("dim1", "all"):
+    p = FusedStencil2D(space, 1, 1, 524288, 1024, 0, 2, with_err=False)
+    p.init_analytic()
+    for _ in range(N):
+        p.step()
+    torch.cuda.synchronize()
+    del p
+if what in ("1d", "all"):
+    p = FusedStencil1D(space, 1 << 27, with_err=False)
+    p.init_analytic()
+    for _ in range(N):
+        p.step()
+    y = p.z[0]
+    o = p.out[0]
+    for v in ("vector", "tma"):
+        for _ in range(N):
+            local.stencil1d(y, 1.0, out=o, variant=v)
+    torch.cuda.synchronize()
+    del p
+if what in ("daxpy", "all"):
+    n = 48 << 20
+    x = torch.rand(n, dtype=torch.float64, device=dev)
+    y = torch.rand(n, dtype=torch.float64, device=dev)
+    for _ in range(N):
+        local.daxpy(1e-9, x, y)
+        local.daxpy_sum(1e-9, x, y)
+    torch.cuda.synchronize()
+print("profile target done")
