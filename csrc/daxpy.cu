@@ -65,17 +65,24 @@ __global__ void __launch_bounds__(kAxpyThreads, 2)
                         double* __restrict__ y, double* out_sum, void* scratch)
 {
   __shared__ double red[32];
-  __shared__ int64_t next;
+  __shared__ int64_t next[2];
   unsigned int* counter = reinterpret_cast<unsigned int*>(scratch) + 1;
   const int64_t nchunks = (n4 + kAxpyChunk - 1) / kAxpyChunk;
   double acc = 0.0;
-  for (;;) {
-    __syncthreads();
-    if (threadIdx.x == 0) next = (int64_t)atomicAdd(counter, 1u);
-    __syncthreads();
-    const int64_t c = next;
-    if (c >= nchunks) break;
+  // the draw for the next chunk is issued before the current chunk is processed, so the
+  // atomic's round trip hides behind the chunk; two smem slots => one barrier per chunk
+  if (threadIdx.x == 0) next[0] = (int64_t)atomicAdd(counter, 1u);
+  __syncthreads();
+  int64_t c = next[0];
+  int slot = 0;
+  while (c < nchunks) {
+    unsigned int prefetched = 0;
+    if (threadIdx.x == 0) prefetched = atomicAdd(counter, 1u);
     axpy_chunk<true>(c * kAxpyChunk, n4, a, x, y, acc);
+    if (threadIdx.x == 0) next[slot ^ 1] = (int64_t)prefetched;
+    __syncthreads();
+    slot ^= 1;
+    c = next[slot];
   }
   if (blockIdx.x == 0) {
     for (int64_t k = 4 * n4 + threadIdx.x; k < n; k += kAxpyThreads) {

@@ -29,18 +29,20 @@ __global__ void __launch_bounds__(kRedThreads, 2)
                 void* scratch, bool vec)
 {
   __shared__ double red[32];
-  __shared__ int64_t next;
+  __shared__ int64_t next[2];
   unsigned int* counter = reinterpret_cast<unsigned int*>(scratch) + 1;
   double acc0 = 0.0, acc1 = 0.0;
   if (vec) {
     const int64_t n4 = n / 4;
     const int64_t nchunks = (n4 + kRedChunk - 1) / kRedChunk;
-    for (;;) {
-      __syncthreads();
-      if (threadIdx.x == 0) next = (int64_t)atomicAdd(counter, 1u);
-      __syncthreads();
-      const int64_t c = next;
-      if (c >= nchunks) break;
+    // next chunk drawn while the current one streams (see daxpy.cu)
+    if (threadIdx.x == 0) next[0] = (int64_t)atomicAdd(counter, 1u);
+    __syncthreads();
+    int64_t c = next[0];
+    int slot = 0;
+    while (c < nchunks) {
+      unsigned int prefetched = 0;
+      if (threadIdx.x == 0) prefetched = atomicAdd(counter, 1u);
       const int64_t i0 = c * kRedChunk + threadIdx.x, i1 = i0 + kRedThreads;
       double4_t u0 = {0, 0, 0, 0}, u1 = u0, w0 = u0, w1 = u0;
       if (i0 < n4) u0 = ldg256_stream(a + 4 * i0);
@@ -56,6 +58,10 @@ __global__ void __launch_bounds__(kRedThreads, 2)
         acc0 += (u0.x + u0.y) + (u0.z + u0.w);
         acc1 += (u1.x + u1.y) + (u1.z + u1.w);
       }
+      if (threadIdx.x == 0) next[slot ^ 1] = (int64_t)prefetched;
+      __syncthreads();
+      slot ^= 1;
+      c = next[slot];
     }
     if (blockIdx.x == 0) {
       for (int64_t k = 4 * n4 + threadIdx.x; k < n; k += kRedThreads) {

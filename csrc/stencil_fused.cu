@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
 {
   __shared__ gmt_halo1d_rank R;
   __shared__ double red[32];
-  __shared__ int64_t next_tile;
+  __shared__ int64_t next_tile[2];
   load_rank(R, ranks + blockIdx.y);
   const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
   const int par = (int)(e & 1);
@@ -75,10 +75,11 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
   }
 
   Sten1d S{R.z, R.out, R.n, R.scale, R.x0, R.dx};
-  // Work is drawn in order from the counter in done[1], kGrab tiles at a time (one atomic and
-  // two barriers per 256 KB of traffic): interior groups first -- they depend on nobody --
-  // then the group(s) holding the edge tiles that need a neighbour's values.
-  constexpr int kGrab = 4;
+  // Work is drawn in order from the counter in done[1]: interior groups first -- they depend
+  // on nobody -- then the group(s) holding the edge tiles that need a neighbour's values.
+  // The draw for the NEXT group is issued before the current one is processed, so the
+  // atomic's round trip to L2 is hidden behind the tile instead of stalling the CTA.
+  constexpr int kGrab = 1;
   const int64_t ntiles = (R.n + kTile1d - 1) / kTile1d;
   const int64_t ngroups = (ntiles + kGrab - 1) / kGrab;
   const int64_t first_int = R.has[0] ? 1 : 0;
@@ -86,12 +87,14 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
   const int64_t n_int = end_int - first_int;
   uint32_t* counter = R.done + 1;
   double err = 0.0;
+  if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
+  __syncthreads();
+  int64_t c = next_tile[0];
+  int slot = 0;
   for (;;) {
-    __syncthreads();
-    if (tid == 0) next_tile = (int64_t)atomicAdd(counter, 1u);
-    __syncthreads();
-    const int64_t c = next_tile;
     if (c >= ngroups) break;
+    unsigned int prefetched = 0;
+    if (tid == 0) prefetched = atomicAdd(counter, 1u);
     int64_t g;
     if (c < n_int) {
       g = first_int + c;
@@ -117,6 +120,12 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
       const int64_t t = g * kGrab + q;
       if (t < ntiles) tile1d<kErr>(S, t * kTile1d, tid, err);
     }
+    // hand the prefetched draw to the CTA through the other slot (its last readers are a
+    // barrier behind), one barrier per tile
+    if (tid == 0) next_tile[slot ^ 1] = (int64_t)prefetched;
+    __syncthreads();
+    slot ^= 1;
+    c = next_tile[slot];
   }
   // 4. epilogue: error norm, then advance the epoch once every CTA of this rank is done
   if (kErr) {
@@ -171,7 +180,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   constexpr int TJ = tile_j<GY>();
   __shared__ gmt_halo2d_rank R;
   __shared__ double red[32];
-  __shared__ int64_t next_tile;
+  __shared__ int64_t next_tile[2];
   load_rank(R, ranks + blockIdx.y);
   const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
   const int par = (int)(e & 1);
@@ -255,12 +264,15 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
   uint32_t* counter = R.done + 1;
   double err = 0.0;
+  if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
+  __syncthreads();
+  int64_t c = next_tile[0];
+  int slot = 0;
   for (;;) {
-    __syncthreads();
-    if (tid == 0) next_tile = (int64_t)atomicAdd(counter, 1u);
-    __syncthreads();
-    const int64_t c = next_tile;
     if (c >= ntiles) break;
+    // draw the next tile now, use it after this one: the atomic's latency hides behind the tile
+    unsigned int prefetched = 0;
+    if (tid == 0) prefetched = atomicAdd(counter, 1u);
     int64_t ti, tj;
     decode_tile(M, c, ti, tj);
     const int64_t i0 = ti * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
@@ -296,6 +308,10 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
       __syncthreads();
     }
     tile2d<GX, GY, kErr>(S, i0, j0, j1, tid, err);
+    if (tid == 0) next_tile[slot ^ 1] = (int64_t)prefetched;
+    __syncthreads();
+    slot ^= 1;
+    c = next_tile[slot];
   }
   if (kErr) {
     const double part = block_sum(err, red);
