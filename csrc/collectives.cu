@@ -30,7 +30,7 @@ struct CollShared {
   double* stage[GMT_COLL_MAX_WORLD];
   uint64_t* flag[GMT_COLL_MAX_WORLD];
   double red[32];
-  int64_t next;
+  int64_t next[2];
   bool last;
 };
 
@@ -154,8 +154,10 @@ __global__ void __launch_bounds__(kCollThreads, 2)
           multimem_st_32B(S.R.mc_buf + off + 4 * v, a);
           if (two) multimem_st_32B(S.R.mc_buf + off + 4 * (v + stride), b);
         } else if (all) {
-          for (int p = 0; p < W; ++p) {
-            if (p == r && !from_in) continue;
+          // peers visited starting at r+1: at any moment the ranks target a permutation of
+          // destinations instead of all hammering the same GPU's ingress port
+          for (int k = from_in ? 0 : 1; k < W; ++k) {
+            const int p = (r + k) % W;
             stg256(S.buf[p] + off + 4 * v, a);
             if (two) stg256(S.buf[p] + off + 4 * (v + stride), b);
           }
@@ -232,7 +234,7 @@ __device__ __forceinline__ void reduce_tail(CollShared& S, uint64_t e, int64_t n
     for (int64_t i = lo + t0; i < hi; i += stride) {
       double s = 0.0;
       for (int p = 0; p < W; ++p) s += ld_peer_f64(S.stage[p] + in_off + i);
-      for (int p = 0; p < W; ++p) S.stage[p][res_off + i] = s;
+      for (int k = 0; k < W; ++k) S.stage[(r + k) % W][res_off + i] = s;
     }
     if (arrive_last(S, S.R.done + 1)) signal_all(S, 1, e);
     wait_all(S, 1, e);
@@ -321,12 +323,14 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   if (aligned(x, 32) && aligned(y, 32)) {
     const int64_t n4 = n / 4, nchunks = (n4 + kDaChunk - 1) / kDaChunk;
     uint32_t* counter = S.R.done + 3;
-    for (;;) {
-      __syncthreads();
-      if (threadIdx.x == 0) S.next = (int64_t)atomicAdd(counter, 1u);
-      __syncthreads();
-      const int64_t c = S.next;
-      if (c >= nchunks) break;
+    // next chunk drawn while the current one streams (see daxpy.cu)
+    if (threadIdx.x == 0) S.next[0] = (int64_t)atomicAdd(counter, 1u);
+    __syncthreads();
+    int64_t c = S.next[0];
+    int slot = 0;
+    while (c < nchunks) {
+      unsigned int prefetched = 0;
+      if (threadIdx.x == 0) prefetched = atomicAdd(counter, 1u);
       double4_t xv[kDaUnroll], yv[kDaUnroll];
 #pragma unroll
       for (int u = 0; u < kDaUnroll; ++u) {
@@ -348,6 +352,10 @@ __global__ void __launch_bounds__(kCollThreads, 2)
           acc += (yv[u].x + yv[u].y) + (yv[u].z + yv[u].w);
         }
       }
+      if (threadIdx.x == 0) S.next[slot ^ 1] = (int64_t)prefetched;
+      __syncthreads();
+      slot ^= 1;
+      c = S.next[slot];
     }
     if (blockIdx.x == 0) {
       for (int64_t k = 4 * n4 + threadIdx.x; k < n; k += kCollThreads) {
@@ -421,7 +429,7 @@ int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, in
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_allgather_f64: bad argument");
   int grid = 0, root = -1;
   const void* k = (const void*)gather_kernel;
-  int rc = coll_grid(k, (n / 4 + kCollThreads * 2 - 1) / (kCollThreads * 2) + 1, n_ranks, &grid);
+  int rc = coll_grid(k, (n / 4 + kCollThreads - 1) / kCollThreads + 1, n_ranks, &grid);
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&from_in, (void*)&use_multicast, (void*)&root};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));
@@ -433,7 +441,7 @@ int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int r
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0 && root >= 0, GMT_EINVAL, "gmt_gather_f64: bad argument");
   int grid = 0, from_in = 0, use_mc = 0;
   const void* k = (const void*)gather_kernel;
-  int rc = coll_grid(k, (n / 4 + kCollThreads * 2 - 1) / (kCollThreads * 2) + 1, n_ranks, &grid);
+  int rc = coll_grid(k, (n / 4 + kCollThreads - 1) / kCollThreads + 1, n_ranks, &grid);
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&from_in, (void*)&use_mc, (void*)&root};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));

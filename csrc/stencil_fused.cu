@@ -27,6 +27,28 @@
 
 namespace gmt {
 
+// Test hook (tests/test_gpu_stress.py): when non-zero, every halo flag store is preceded by a
+// pseudo-random sleep of up to this many nanoseconds, so that chunks arrive late, out of order
+// and at different times on different ranks -- the race test the reference never needed because
+// it synchronises the whole device around every exchange (mpi_stencil2d_gt.cc:202,254).
+__device__ unsigned int g_debug_push_delay_ns = 0;
+
+__device__ __forceinline__ void debug_delay(uint64_t salt)
+{
+  const unsigned int mx = g_debug_push_delay_ns;
+  if (mx == 0) return;
+  unsigned int h = (unsigned int)(salt * 2654435761ull) ^ (unsigned int)clock64();
+  h ^= h >> 13;
+  h *= 0x5bd1e995u;
+  h ^= h >> 15;
+  unsigned int ns = h % mx;
+  while (ns > 0) {
+    const unsigned int step = ns < 100000u ? ns : 100000u;
+    __nanosleep(step);
+    ns -= step;
+  }
+}
+
 template <typename RankT>
 __device__ __forceinline__ void load_rank(RankT& dst, const RankT* src)
 {
@@ -70,6 +92,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
       const double2 v = ldg128(s == 0 ? R.z + 2 : R.z + R.n);
       stg128(R.peer_inbox[s][par], v);
       fence_sys();
+      debug_delay(e * 131 + blockIdx.y * 7 + s);
       st_release_sys(R.peer_flag[s], e);
     }
   }
@@ -255,6 +278,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
       __syncthreads();
       if (tid == 0) {
         fence_sys();
+        debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
         st_release_sys(R.peer_flag[side] + c, e);
       }
     }
@@ -376,6 +400,12 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
     nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
   }
   return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream));
+}
+
+int gmt_debug_set_push_delay(unsigned int max_ns)
+{
+  GMT_CUDA(cudaMemcpyToSymbol(gmt::g_debug_push_delay_ns, &max_ns, sizeof(max_ns)));
+  return 0;
 }
 
 int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny)

@@ -130,6 +130,7 @@ _SIGS = {
     "gmt_fused_stencil1d_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_fused_stencil2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, C.c_int, c_ptr]),
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),
+    "gmt_debug_set_push_delay": (None, [C.c_uint]),
     "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_gather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),

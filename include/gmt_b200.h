@@ -245,6 +245,9 @@ typedef struct {
 
 int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
                             int gx, int gy, int with_err, gmt_stream_t stream);
+/* Test hook: sleep a pseudo-random time of up to max_ns nanoseconds before every halo flag
+ * store (0 = off, the default).  Shakes the flag/epoch/parity protocol in stress tests.   */
+int gmt_debug_set_push_delay(unsigned int max_ns);
 /* flag words needed on `side` for the given interior extents */
 int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
 
