@@ -23,13 +23,14 @@ namespace gmt {
 
 constexpr int kCollThreads = 512;
 constexpr int kRoundStride = 32;  // words per signalling round in a flag block
+constexpr int kLLBase = 64;       // LL slots: [parity][src rank][2 words] after the two rounds
 
 struct CollShared {
   gmt_coll_rank R;
   double* buf[GMT_COLL_MAX_WORLD];
   double* stage[GMT_COLL_MAX_WORLD];
   uint64_t* flag[GMT_COLL_MAX_WORLD];
-  double red[32];
+  double red[40];
   int64_t next[2];
   bool last;
 };
@@ -374,14 +375,39 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   const double part = block_sum(acc, S.red);
   double total;
   if (!grid_sum_last_block(part, S.R.scratch, S.red, total, gridDim.x, blockIdx.x)) return;
-  // last CTA of this rank: one-shot all-reduce of the rank totals
-  if (threadIdx.x == 0) S.stage[r][(int64_t)par * S.R.stage_cap] = total;
+  // Last CTA of this rank: one-shot all-reduce of the W rank totals in "LL" style -- every
+  // 8-byte word carries 32 bits of payload and the 32-bit epoch, so data and flag arrive
+  // together: no fence, no separate flag, no remote read; the cost is ONE one-way NVLink store
+  // latency.  (8-byte stores are single-copy atomic; slots are double-buffered by epoch parity.)
+  if (threadIdx.x == 0) S.red[0] = total;
   __syncthreads();
-  signal_all(S, 0, e);
-  wait_all(S, 0, e);
+  const uint64_t e32 = e & 0xffffffffull;
+  bool ok = true;
+  if ((int)threadIdx.x < W) {
+    const uint64_t bits = (uint64_t)__double_as_longlong(S.red[0]);
+    uint64_t* dst = S.flag[threadIdx.x] + kLLBase + ((int64_t)par * GMT_COLL_MAX_WORLD + r) * 2;
+    st_relaxed_sys(dst, (bits & 0xffffffffull) | (e32 << 32));
+    st_relaxed_sys(dst + 1, (bits >> 32) | (e32 << 32));
+    const uint64_t* src = S.flag[r] + kLLBase + ((int64_t)par * GMT_COLL_MAX_WORLD + threadIdx.x) * 2;
+    const int64_t limit = S.R.spin_limit > 0 ? S.R.spin_limit : kDefaultSpinLimit;
+    uint64_t w0 = 0, w1 = 0;
+    ok = false;
+    for (int64_t it = 0; it < limit; ++it) {
+      w0 = ld_relaxed_sys(src);
+      w1 = ld_relaxed_sys(src + 1);
+      if ((w0 >> 32) == e32 && (w1 >> 32) == e32) {
+        ok = true;
+        break;
+      }
+      if (it > 64) __nanosleep(32);
+    }
+    if (!ok) atomicExch(S.R.status, 1u + threadIdx.x);
+    S.red[1 + threadIdx.x] = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
     double s = 0.0;
-    for (int p = 0; p < W; ++p) s += ld_peer_f64(S.stage[p] + (int64_t)par * S.R.stage_cap);
+    for (int p = 0; p < W; ++p) s += S.red[1 + p];  // rank order: same bits on every rank
     *S.R.out = s;
   }
   coll_finish(S, e);

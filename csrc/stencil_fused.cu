@@ -32,6 +32,7 @@ namespace gmt {
 // and at different times on different ranks -- the race test the reference never needed because
 // it synchronises the whole device around every exchange (mpi_stencil2d_gt.cc:202,254).
 __device__ unsigned int g_debug_push_delay_ns = 0;
+static unsigned int g_debug_push_delay_host = 0;  // launchers pick the kDebug instantiation when set
 
 __device__ __forceinline__ void debug_delay(uint64_t salt)
 {
@@ -74,7 +75,7 @@ __device__ __forceinline__ void finish_epoch(uint32_t* done, uint64_t* epoch, ui
 }
 
 // ====================================================================== 1-D
-template <bool kErr>
+template <bool kErr, bool kDebug>
 __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d_rank* __restrict__ ranks)
 {
   __shared__ gmt_halo1d_rank R;
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
       const double2 v = ldg128(s == 0 ? R.z + 2 : R.z + R.n);
       stg128(R.peer_inbox[s][par], v);
       fence_sys();
-      debug_delay(e * 131 + blockIdx.y * 7 + s);
+      if (kDebug) debug_delay(e * 131 + blockIdx.y * 7 + s);
       st_release_sys(R.peer_flag[s], e);
     }
   }
@@ -197,7 +198,7 @@ __device__ __forceinline__ void decode_tile(const TileMap& M, int64_t c, int64_t
   }
 }
 
-template <int GX, int GY, bool kErr>
+template <int GX, int GY, bool kErr, bool kDebug>
 __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
 {
   constexpr int TJ = tile_j<GY>();
@@ -278,7 +279,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
       __syncthreads();
       if (tid == 0) {
         fence_sys();
-        debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
+        if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
         st_release_sys(R.peer_flag[side] + c, e);
       }
     }
@@ -312,14 +313,14 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
         if (!wait_flag_ge(f, e, R.spin_limit)) atomicExch(R.status, 1u + tid);
       }
       __syncthreads();
-      if (sides & 3) {
+      if (sides & 3) {  // x-face ghost rows: inbox -> the array's own ghost cells
         for (int64_t j = j0 + tid; j < j1; j += kStThreads) {
           double* col = R.z + (j + GY) * ldz;
           if (sides & 1) stg128(col, ld_peer_f64x2(R.my_inbox[0][par] + 2 * j));
           if (sides & 2) stg128(col + nx + 2, ld_peer_f64x2(R.my_inbox[1][par] + 2 * j));
         }
       }
-      if (sides & 12) {
+      if (sides & 12) {  // y-face ghost columns are landed in the array first (few tiles)
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
           for (int64_t i = i0 + 2 * tid; i < i1; i += 2 * kStThreads) {
@@ -374,7 +375,9 @@ int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64
   using namespace gmt;
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n > 0, GMT_EINVAL, "gmt_fused_stencil1d_f64: bad argument");
   GMT_REQUIRE(n % 2 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil1d_f64: n must be even (16-byte halo stores)");
-  const void* k = with_err ? (const void*)fused1d_kernel<true> : (const void*)fused1d_kernel<false>;
+  const bool dbg = g_debug_push_delay_host != 0;
+  const void* k = dbg ? (with_err ? (const void*)fused1d_kernel<true, true> : (const void*)fused1d_kernel<false, true>)
+                      : (with_err ? (const void*)fused1d_kernel<true, false> : (const void*)fused1d_kernel<false, false>);
   return launch_fused(k, ranks_dev, n_ranks, (n + 4 * kTile1d - 1) / (4 * kTile1d), as_stream(stream));
 }
 
@@ -389,22 +392,28 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   const void* k = nullptr;
   const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
   int64_t nt = 0;
+  const bool dbg = g_debug_push_delay_host != 0;
+#define GMT_PICK(GX_, GY_)                                                                                   \
+  (dbg ? (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, true> : (const void*)fused2d_kernel<GX_, GY_, false, true>) \
+       : (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, false> : (const void*)fused2d_kernel<GX_, GY_, false, false>))
   if (gx && !gy) {
-    k = with_err ? (const void*)fused2d_kernel<2, 0, true> : (const void*)fused2d_kernel<2, 0, false>;
+    k = GMT_PICK(2, 0);
     nt = tiles_i * ((ny + kTileJx - 1) / kTileJx);
   } else if (!gx && gy) {
-    k = with_err ? (const void*)fused2d_kernel<0, 2, true> : (const void*)fused2d_kernel<0, 2, false>;
+    k = GMT_PICK(0, 2);
     nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
   } else {
-    k = with_err ? (const void*)fused2d_kernel<2, 2, true> : (const void*)fused2d_kernel<2, 2, false>;
+    k = GMT_PICK(2, 2);
     nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
   }
+#undef GMT_PICK
   return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream));
 }
 
 int gmt_debug_set_push_delay(unsigned int max_ns)
 {
   GMT_CUDA(cudaMemcpyToSymbol(gmt::g_debug_push_delay_ns, &max_ns, sizeof(max_ns)));
+  gmt::g_debug_push_delay_host = max_ns;
   return 0;
 }
 

@@ -10,6 +10,7 @@
 //     thread in flight) so that ~128 KB per SM is outstanding at 2 CTAs/SM.
 #pragma once
 #include "common.cuh"
+#include "p2p.cuh"
 
 namespace gmt {
 

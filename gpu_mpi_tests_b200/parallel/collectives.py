@@ -19,7 +19,7 @@ from ..ops._lib import CollRank, lib
 from .symm import PeerSpace
 
 F64 = torch.float64
-FLAG_WORDS = 64
+FLAG_WORDS = 256
 MAX_WORLD = 32
 
 

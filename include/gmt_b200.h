@@ -257,10 +257,11 @@ int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
  * production, all ranks in one cooperative launch when emulated on a single GPU.
  *
  * Signalling: every rank owns a flag block of GMT_COLL_FLAG_WORDS words; word [round*32 + src]
- * holds the last epoch rank `src` signalled for that round (st.release.sys / ld.acquire.sys,
- * bounded spins).  Epochs only grow; reduction inputs travel through a staging area that is
+ * (rounds 0,1) holds the last epoch rank `src` signalled for that round (st.release.sys /
+ * ld.acquire.sys, bounded spins); words [64 + (parity*32 + src)*2 ..] are "LL" slots in which a
+ * scalar travels as two 8-byte words that each carry 32 payload bits and the 32-bit epoch.  Epochs only grow; reduction inputs travel through a staging area that is
  * double-buffered by epoch parity, so a rank that is one call ahead cannot disturb a slower one. */
-#define GMT_COLL_FLAG_WORDS 64
+#define GMT_COLL_FLAG_WORDS 256
 #define GMT_COLL_MAX_WORLD 32
 typedef struct {
   int32_t rank, world;
