@@ -142,6 +142,11 @@ inline int sm_count()
   return cached;
 }
 
+// Zero-initialised, self-resetting work counters (4 x u32) private to (device, stream), for
+// persistent kernels whose entry point has no scratch parameter.  Allocated on first use and
+// kept for the life of the process (defined in runtime.cu).
+int stream_counters(cudaStream_t stream, unsigned int** out);
+
 inline cudaStream_t as_stream(gmt_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 template <typename T>

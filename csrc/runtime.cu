@@ -14,6 +14,33 @@
 
 #include "common.cuh"
 
+#include <map>
+#include <mutex>
+#include <utility>
+
+namespace gmt {
+
+int stream_counters(cudaStream_t stream, unsigned int** out)
+{
+  static std::mutex mu;
+  static std::map<std::pair<int, cudaStream_t>, unsigned int*> table;
+  int dev = 0;
+  GMT_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(dev, stream);
+  auto it = table.find(key);
+  if (it == table.end()) {
+    unsigned int* p = nullptr;
+    GMT_CUDA(cudaMalloc(&p, 64));
+    GMT_CUDA(cudaMemset(p, 0, 64));
+    it = table.emplace(key, p).first;
+  }
+  *out = it->second;
+  return 0;
+}
+
+}  // namespace gmt
+
 extern "C" {
 
 const char* gmt_last_error(void) { return gmt::err_buf(); }

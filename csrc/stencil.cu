@@ -12,6 +12,9 @@
 
 #include "stencil_tiles.cuh"
 
+extern "C" int gmt_stencil2d_d1_cluster_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,
+                                            int64_t ldo, double scale, gmt_stream_t stream);
+
 namespace gmt {
 
 // ============================================================== variant 0
@@ -137,6 +140,8 @@ static int launch_plain2d(int gx, int gy, int64_t nx, int64_t ny, const double* 
   GMT_REQUIRE(nx > 0 && ny > 0 && z && out, GMT_EINVAL, "stencil2d: bad argument");
   GMT_REQUIRE(ldz >= nx + 2 * gx && ldo >= nx, GMT_EINVAL, "stencil2d: leading dimension too small");
   GMT_REQUIRE(variant >= 0 && variant <= 2, GMT_EINVAL, "stencil2d: unknown variant %d", variant);
+  if (variant == 2 && !gx && gy && vec2d_ok(nx, z, ldz, out, ldo))
+    return gmt_stencil2d_d1_cluster_f64(nx, ny, z, ldz, out, ldo, sy, (gmt_stream_t)st);
   if (variant == 0 || !vec2d_ok(nx, z, ldz, out, ldo)) {
     int64_t want = (nx * ny + 255) / 256;
     int grid = (int)std::min<int64_t>(want, (int64_t)sm_count() * 8);

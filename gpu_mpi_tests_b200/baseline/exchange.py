@@ -42,6 +42,29 @@ def _sync(device: torch.device) -> None:
         torch.cuda.synchronize(device)
 
 
+class CommError(RuntimeError):
+    """A communication-library call failed: the analogue of a non-MPI_SUCCESS return code caught
+    by the reference's check() (mpi_stencil2d_gt.cc:32-40), which prints `file:line error code`
+    and exits with status 2."""
+
+    def __init__(self, where: str, code: int, detail: str):
+        super().__init__(f"{where} error {code}: {detail}")
+        self.where, self.code = where, code
+
+
+def comm_check(fn, *args, **kwargs):
+    """CHECK(x) for library communication calls: re-raise failures as CommError carrying the call
+    site, so that the CLI programs can print the reference's line and exit(2)."""
+    import inspect
+    try:
+        return fn(*args, **kwargs)
+    except CommError:
+        raise
+    except Exception as e:  # noqa: BLE001
+        fr = inspect.stack()[1]
+        raise CommError(f"{fr.filename.rsplit('/', 1)[-1]}:{fr.lineno}", 1, repr(e)) from e
+
+
 def exchange_pairs(sends: list, recvs: list, group=None) -> None:
     """Post all receives and sends (MPI_Irecv/MPI_Isend), then wait for all (MPI_Waitall).
     sends/recvs: lists of (tensor, peer_rank)."""
@@ -49,8 +72,12 @@ def exchange_pairs(sends: list, recvs: list, group=None) -> None:
     ops += [dist.P2POp(dist.isend, t, p, group=group) for (t, p) in sends]
     if not ops:
         return
-    for w in dist.batch_isend_irecv(ops):
-        w.wait()
+
+    def run():
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+    comm_check(run)
 
 
 class BaselineStencil1D:

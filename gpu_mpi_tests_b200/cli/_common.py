@@ -54,3 +54,15 @@ def getenv_memory_per_core(rt, out) -> None:
     """Rank 0 echoes MEMORY_PER_CORE (mpi_daxpy.cc:101-108)."""
     if rt.rank == 0:
         out(report.memory_per_core(os.environ.get("MEMORY_PER_CORE")))
+
+
+def run_main(body) -> int:
+    """Wrap a program body: a failed communication call prints `file:line error code` and exits
+    with status 2, like the reference's check() (mpi_stencil2d_gt.cc:32-40)."""
+    from ..baseline.exchange import CommError
+    try:
+        return body()
+    except CommError as e:
+        where, _, line = e.where.partition(":")
+        print(report.mpi_error(where, int(line or 0), e.code), flush=True)
+        sys.exit(2)

@@ -132,7 +132,7 @@ def test_sum(rt, out, impl, space, dim, mem, n_local_deriv, n_other, n_iter, n_w
         out(report.test_sum_line(dim, mem, time_sum))
 
 
-def main(argv=None) -> int:
+def _main(argv=None) -> int:
     ap = _common.base_parser(__doc__)
     ap.add_argument("n_local_deriv", nargs="?", type=int, default=1024)
     ap.add_argument("n_iter", nargs="?", type=int, default=1000)
@@ -158,6 +158,10 @@ def main(argv=None) -> int:
                      args.debug)
     _common.finish(rt)
     return 0
+
+
+def main(argv=None) -> int:
+    return _common.run_main(lambda: _main(argv))
 
 
 if __name__ == "__main__":

@@ -73,7 +73,7 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
         out(report.oo_err_norm(r, rt.vendor_id, err))
 
 
-def main(argv=None) -> int:
+def _main(argv=None) -> int:
     ap = _common.base_parser(__doc__)
     ap.add_argument("nx_local", nargs="?", type=int, default=1024)
     ap.add_argument("stage_host", nargs="?", default="0")
@@ -92,6 +92,10 @@ def main(argv=None) -> int:
     run_dim0(rt, out, impl, args.nx_local, args.ny, args.n_iter, n_warmup, stage_host, "sycl")
     _common.finish(rt)
     return 0
+
+
+def main(argv=None) -> int:
+    return _common.run_main(lambda: _main(argv))
 
 
 if __name__ == "__main__":

@@ -11,7 +11,7 @@ from . import _common
 from .mpi_stencil2d_sycl import run_dim0
 
 
-def main(argv=None) -> int:
+def _main(argv=None) -> int:
     ap = _common.base_parser(__doc__)
     ap.add_argument("n_global_ki", nargs="?", type=int, default=8)
     ap.add_argument("stage_host", nargs="?", default="0")
@@ -33,6 +33,10 @@ def main(argv=None) -> int:
     run_dim0(rt, out, impl, slab.n_local, n_global, n_iter, n_warmup, stage_host, "oo")
     _common.finish(rt)
     return 0
+
+
+def main(argv=None) -> int:
+    return _common.run_main(lambda: _main(argv))
 
 
 if __name__ == "__main__":

@@ -17,7 +17,7 @@ from ..utils import report
 from . import _common
 
 
-def main(argv=None) -> int:
+def _main(argv=None) -> int:
     ap = _common.base_parser(__doc__)
     ap.add_argument("n_global_mi", nargs="?", type=int, default=32)
     ap.add_argument("--points", type=int, default=None, help="n_global in points (overrides the Mi argument)")
@@ -53,6 +53,10 @@ def main(argv=None) -> int:
     out(report.err_norm_line(r, rt.world_size, rt.device_id, rt.vendor_id, err))
     _common.finish(rt)
     return 0
+
+
+def main(argv=None) -> int:
+    return _common.run_main(lambda: _main(argv))
 
 
 if __name__ == "__main__":

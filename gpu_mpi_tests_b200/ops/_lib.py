@@ -122,6 +122,7 @@ _SIGS = {
     "gmt_iota_f64": (None, [c_i64, c_dbl, c_dbl, c_dbl, c_ptr, c_ptr]),
     "gmt_stencil1d_f64": (None, [c_i64, c_ptr, c_ptr, c_dbl, C.c_int, c_ptr]),
     "gmt_stencil2d_f64": (None, [C.c_int, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, C.c_int, c_ptr]),
+    "gmt_stencil2d_d1_cluster_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, c_ptr]),
     "gmt_stencil2d_xy_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, c_dbl, c_ptr]),
     "gmt_copy2d_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr]),
     "gmt_init_stencil1d_f64": (None, [c_i64, C.c_int, c_dbl, c_dbl, c_ptr, c_ptr, C.c_int, C.c_int, c_ptr]),

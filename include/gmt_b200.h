@@ -141,7 +141,9 @@ int gmt_iota_f64(int64_t n, double start, double step, double mul, double* x, gm
  * (stencil1d_5, mpi_stencil_gt.cc:54-59).  in has n+4 elements.
  * variant: 0 = one thread per point (mirrors a generic expression kernel),
  *          1 = 256-bit vectorised streaming kernel,
- *          2 = TMA bulk-copy (cp.async.bulk + mbarrier) pipelined kernel.    */
+ *          2 = TMA: cp.async.bulk + mbarrier pipeline (1-D); for the 2-D dim-1 stencil,
+ *              tensor-map loads + 2-CTA clusters sharing halo columns over DSMEM
+ *              (2-D dim 0 has no TMA variant and runs variant 1).             */
 int gmt_stencil1d_f64(int64_t n, const double* in, double* out, double scale, int variant,
                       gmt_stream_t stream);
 /* same stencil applied along dim 0 (contiguous) or dim 1 (strided) of a column-major
@@ -150,6 +152,11 @@ int gmt_stencil1d_f64(int64_t n, const double* in, double* out, double scale, in
  * (stencil2d_1d_5_d0/_d1, mpi_stencil2d_gt.cc:84-110)                        */
 int gmt_stencil2d_f64(int dim, int64_t nx, int64_t ny, const double* z, int64_t ldz, double* dz,
                       int64_t lddz, double scale, int variant, gmt_stream_t stream);
+/* variant 2 of the dim-1 stencil on its own: 2-D TMA tensor-map loads + thread-block clusters
+ * of two CTAs sharing their halo columns over distributed shared memory (no reference
+ * counterpart; see csrc/stencil_tma.cu for the shape/alignment requirements)            */
+int gmt_stencil2d_d1_cluster_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,
+                                 int64_t ldo, double scale, gmt_stream_t stream);
 /* cross stencil on a (nx+4, ny+4) array ghosted in both dims:
  * out(i,j) = sx * d/dx + sy * d/dy   (BASELINE config 3, no reference counterpart) */
 int gmt_stencil2d_xy_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,

@@ -71,7 +71,7 @@ def test_stencil1d(dev, variant, n):
     assert rel(got, ref) < TOL
 
 
-@pytest.mark.parametrize("variant", ["generic", "vector"])
+@pytest.mark.parametrize("variant", ["generic", "vector", "tma"])
 @pytest.mark.parametrize("shape", [(8, 8), (1024, 64), (2048, 130), (12, 7), (4096, 257), (1028, 33), (10, 5)])
 def test_stencil2d(dev, variant, shape):
     nx, ny = shape
@@ -81,6 +81,20 @@ def test_stencil2d(dev, variant, shape):
     assert rel(local.stencil2d(z1, 1, 2.5, variant=variant), oracle.stencil2d_1d_5(z1, 1, 2.5)) < TOL
     zz = torch.rand(ny + 4, nx + 4, dtype=F64, device=dev)
     assert rel(local.stencil2d_xy(zz, 2.5, 1.5), oracle.stencil2d_xy(zz, 2.5, 1.5)) < TOL
+
+
+@pytest.mark.parametrize("shape", [(1024, 64), (2048, 130), (4096, 257), (1028, 33), (8, 8), (12, 7), (5120, 16)])
+def test_stencil2d_dim1_tma_cluster_variant(dev, shape):
+    """2-D tensor-map TMA loads + 2-CTA clusters with DSMEM halo sharing vs the fp64 reference."""
+    nx, ny = shape
+    z1 = torch.rand(ny + 4, nx, dtype=F64, device=dev)
+    ref = oracle.stencil2d_1d_5(z1, 1, 2.5)
+    out = torch.full((ny, nx), -7.0, dtype=F64, device=dev)
+    local.stencil2d(z1, 1, 2.5, out=out, variant="tma")
+    assert rel(out, ref) < TOL
+    # twice in a row on the same stream (barrier phases, stage reuse)
+    local.stencil2d(z1, 1, 2.5, out=out, variant="tma")
+    assert rel(out, ref) < TOL
 
 
 def test_stencil2d_padded_leading_dimension(dev):

@@ -325,3 +325,24 @@ if "--no-timing" not in sys.argv:
 
 (OUT / "probe.json").write_text(json.dumps(res, indent=1))
 print("probe done")
+
+# ---- TMA / cluster variants at benchmark shapes (appended probe)
+if "--tma" in sys.argv:
+    from gpu_mpi_tests_b200.ops import local as _local
+    T2 = {}
+    n = 1 << 27
+    yin = torch.rand(n + 4, dtype=f64, device=dev)
+    o = torch.empty(n, dtype=f64, device=dev)
+    for v in ("vector", "tma"):
+        r = timeit(lambda: _local.stencil1d(yin, 1.0, out=o, variant=v))
+        T2[f"sten1d_{v}"] = {"ms": r["min_ms"], "GLUPs": n / r["min_ms"] / 1e6}
+    del yin, o
+    for (nx, ny) in ((524288, 1024), (16384, 16384)):
+        z = torch.rand(ny + 4, nx, dtype=f64, device=dev)
+        o = torch.empty(ny, nx, dtype=f64, device=dev)
+        for v in ("vector", "tma"):
+            r = timeit(lambda: _local.stencil2d(z, 1, 1.0, out=o, variant=v))
+            T2[f"sten2d_d1_{v}_{nx}x{ny}"] = {"ms": r["min_ms"], "GLUPs": nx * ny / r["min_ms"] / 1e6}
+        del z, o
+    print(json.dumps(T2, indent=1))
+    (OUT / "probe_tma.json").write_text(json.dumps(T2, indent=1))
