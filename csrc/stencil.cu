@@ -62,9 +62,8 @@ __global__ void __launch_bounds__(kStThreads, 2) stencil1d_vec_kernel(Sten1d S)
 }
 
 template <int GX, int GY>
-__global__ void __launch_bounds__(kStThreads, 2) stencil2d_vec_kernel(Sten2d S, int64_t tiles_i)
+__global__ void __launch_bounds__(kStThreads, 2) stencil2d_vec_kernel(Sten2d S, int64_t tiles_i, int TJ)
 {
-  constexpr int TJ = tile_j<GY>();
   const int64_t t = blockIdx.x;
   const int64_t tj = t / tiles_i, ti = t - tj * tiles_i;
   const int64_t j0 = tj * TJ;
@@ -151,15 +150,16 @@ static int launch_plain2d(int gx, int gy, int64_t nx, int64_t ny, const double* 
   }
   Sten2d S{z, out, nx, ny, ldz, ldo, sx, sy, 0, 0, 0, 0};
   const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
-  const int64_t nt = tiles_i * ((ny + (gy ? kTileJy : kTileJx) - 1) / (gy ? kTileJy : kTileJx));
+  const int tj = runtime_tile_j(gx, gy, false);
+  const int64_t nt = tiles_i * ((ny + tj - 1) / tj);
   GMT_REQUIRE(nt < (1LL << 31), GMT_ETOOBIG, "stencil2d: array too large for a one-shot grid");
   const int grid = (int)nt;
   if (gx && !gy) {
-    stencil2d_vec_kernel<2, 0><<<grid, kStThreads, 0, st>>>(S, tiles_i);
+    stencil2d_vec_kernel<2, 0><<<grid, kStThreads, 0, st>>>(S, tiles_i, tj);
   } else if (!gx && gy) {
-    stencil2d_vec_kernel<0, 2><<<grid, kStThreads, 0, st>>>(S, tiles_i);
+    stencil2d_vec_kernel<0, 2><<<grid, kStThreads, 0, st>>>(S, tiles_i, tj);
   } else {
-    stencil2d_vec_kernel<2, 2><<<grid, kStThreads, 0, st>>>(S, tiles_i);
+    stencil2d_vec_kernel<2, 2><<<grid, kStThreads, 0, st>>>(S, tiles_i, tj);
   }
   GMT_LAUNCH_CHECK();
   return 0;

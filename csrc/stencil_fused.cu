@@ -162,6 +162,73 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
   finish_epoch(R.done, R.epoch, e, 2);
 }
 
+// ---------------- export of the boundary chunks.  x faces: kFlagCols columns x 2 rows
+// (strided 16-byte pieces gathered into a contiguous inbox); y faces: kTileI rows x 2 columns.
+// Only the first kPushCtas CTAs export (then join the tile loop late); everybody else starts
+// computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
+// each followed by its own fence + flag, so the exchange streams underneath the sweep: the
+// export front moves ~10x faster than the compute front.
+template <int GX, int GY, bool kDebug>
+__device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i)
+{
+  const int tid = threadIdx.x;
+  const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
+  constexpr int kPushCtas = 32;
+  const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
+  const int64_t nfy = GY ? tiles_i : 0;
+  const int64_t nunits = 2 * (nfx + nfy);
+  const int npush = min((int)gridDim.x, kPushCtas);
+  if ((int)blockIdx.x >= npush) return;
+  for (int64_t u = blockIdx.x; u < nunits; u += npush) {
+    int side;
+    int64_t c;
+    if (u < 2 * nfx) {
+      side = (int)(u & 1);
+      c = u >> 1;
+    } else {
+      side = 2 + (int)((u - 2 * nfx) & 1);
+      c = (u - 2 * nfx) >> 1;
+    }
+    if (!R.has[side]) continue;  // CTA-uniform
+    double* box = R.peer_inbox[side][par];
+    if (side < 2) {
+      const int64_t j0 = c * kFlagCols;
+      const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
+      double2 v[kFlagCols / kStThreads];
+#pragma unroll
+      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) v[q] = ldg128(src + j * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) stg128(box + 2 * j, v[q]);
+      }
+    } else {
+      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+      const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
+      double2 v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      fence_sys();
+      if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
+      st_release_sys(R.peer_flag[side] + c, e);
+    }
+  }
+}
+
 // ====================================================================== 2-D
 struct TileMap {
   int64_t tiles_i, tiles_j, a0, a1, b0, b1, ni, nj, n_int;
@@ -199,9 +266,8 @@ __device__ __forceinline__ void decode_tile(const TileMap& M, int64_t c, int64_t
 }
 
 template <int GX, int GY, bool kErr, bool kDebug>
-__global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
+__global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d_rank* __restrict__ ranks, int TJ)
 {
-  constexpr int TJ = tile_j<GY>();
   __shared__ gmt_halo2d_rank R;
   __shared__ double red[32];
   __shared__ int64_t next_tile[2];
@@ -222,82 +288,20 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   M.n_int = M.ni * M.nj;
   const int64_t ntiles = M.tiles_i * M.tiles_j;
 
-  // ---------------- phase 1: export boundary chunks.  x faces: kFlagCols columns x 2 rows
-  // (strided 16-byte pieces gathered into a contiguous inbox); y faces: kTileI rows x 2 columns.
-  // Only the first kPushCtas CTAs export (then join the tile loop late); everybody else starts
-  // computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
-  // each followed by its own fence + flag, so the exchange streams underneath the sweep: the
-  // export front moves ~10x faster than the compute front and only the very first chunk's
-  // latency can ever be exposed.
-  constexpr int kPushCtas = 32;
-  const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
-  const int64_t nfy = GY ? M.tiles_i : 0;
-  const int64_t nunits = 2 * (nfx + nfy);
-  const int npush = min((int)gridDim.x, kPushCtas);
-  if ((int)blockIdx.x < npush) {
-    for (int64_t u = blockIdx.x; u < nunits; u += npush) {
-      int side;
-      int64_t c;
-      if (u < 2 * nfx) {
-        side = (int)(u & 1);
-        c = u >> 1;
-      } else {
-        side = 2 + (int)((u - 2 * nfx) & 1);
-        c = (u - 2 * nfx) >> 1;
-      }
-      if (!R.has[side]) continue;  // CTA-uniform
-      double* box = R.peer_inbox[side][par];
-      if (side < 2) {
-        const int64_t j0 = c * kFlagCols;
-        const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
-        double2 v[kFlagCols / kStThreads];
-#pragma unroll
-        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-          const int64_t j = j0 + tid + q * kStThreads;
-          if (j < ny) v[q] = ldg128(src + j * ldz);
-        }
-#pragma unroll
-        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-          const int64_t j = j0 + tid + q * kStThreads;
-          if (j < ny) stg128(box + 2 * j, v[q]);
-        }
-      } else {
-        const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
-        const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
-        double2 v[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
-          if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
-          if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
-        }
-      }
-      __syncthreads();
-      if (tid == 0) {
-        fence_sys();
-        if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
-        st_release_sys(R.peer_flag[side] + c, e);
-      }
-    }
-  }
+  push_faces<GX, GY, kDebug>(R, e, par, M.tiles_i);
 
   // ---------------- phase 2: tiles from the shared counter
   Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
   uint32_t* counter = R.done + 1;
   double err = 0.0;
-  if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
-  __syncthreads();
-  int64_t c = next_tile[0];
-  int slot = 0;
+  // (no prefetched draw here, unlike the 1-D kernel: 2-D tiles are 0.5-2 MB, the atomic's
+  // latency is noise, and a tile pre-claimed by a still-busy CTA would lengthen the tail)
   for (;;) {
+    __syncthreads();
+    if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
+    __syncthreads();
+    const int64_t c = next_tile[0];
     if (c >= ntiles) break;
-    // draw the next tile now, use it after this one: the atomic's latency hides behind the tile
-    unsigned int prefetched = 0;
-    if (tid == 0) prefetched = atomicAdd(counter, 1u);
     int64_t ti, tj;
     decode_tile(M, c, ti, tj);
     const int64_t i0 = ti * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
@@ -333,10 +337,6 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
       __syncthreads();
     }
     tile2d<GX, GY, kErr>(S, i0, j0, j1, tid, err);
-    if (tid == 0) next_tile[slot ^ 1] = (int64_t)prefetched;
-    __syncthreads();
-    slot ^= 1;
-    c = next_tile[slot];
   }
   if (kErr) {
     const double part = block_sum(err, red);
@@ -350,12 +350,12 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
 
 template <typename RankT>
 static int launch_fused(const void* kernel, const RankT* ranks_dev, int n_ranks, int64_t ntiles,
-                        cudaStream_t st)
+                        cudaStream_t st, int tile_j_arg = 0)
 {
   int grid = 0;
   int rc = persistent_grid(kernel, kStThreads, ntiles, n_ranks, &grid);
   if (rc) return rc;
-  void* args[] = {(void*)&ranks_dev};
+  void* args[] = {(void*)&ranks_dev, (void*)&tile_j_arg};
   if (n_ranks > 1) {
     // several ranks spin on one another inside one launch: co-residency must be guaranteed
     GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(kStThreads), args, 0, st));
@@ -391,6 +391,7 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   GMT_REQUIRE(nx % 4 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil2d_f64: nx must be a multiple of 4");
   const void* k = nullptr;
   const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
+  const int tj = runtime_tile_j(gx, gy, true);
   int64_t nt = 0;
   const bool dbg = g_debug_push_delay_host != 0;
 #define GMT_PICK(GX_, GY_)                                                                                   \
@@ -398,16 +399,16 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
        : (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, false> : (const void*)fused2d_kernel<GX_, GY_, false, false>))
   if (gx && !gy) {
     k = GMT_PICK(2, 0);
-    nt = tiles_i * ((ny + kTileJx - 1) / kTileJx);
+    nt = tiles_i * ((ny + tj - 1) / tj);
   } else if (!gx && gy) {
     k = GMT_PICK(0, 2);
-    nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
+    nt = tiles_i * ((ny + tj - 1) / tj);
   } else {
     k = GMT_PICK(2, 2);
-    nt = tiles_i * ((ny + kTileJy - 1) / kTileJy);
+    nt = tiles_i * ((ny + tj - 1) / tj);
   }
 #undef GMT_PICK
-  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream));
+  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj);
 }
 
 int gmt_debug_set_push_delay(unsigned int max_ns)

@@ -9,6 +9,8 @@
 //   * loads are issued in hand-made batches of 4 columns (up to 8 x 32 B per
 //     thread in flight) so that ~128 KB per SM is outstanding at 2 CTAs/SM.
 #pragma once
+#include <cstdlib>
+
 #include "common.cuh"
 #include "p2p.cuh"
 
@@ -26,6 +28,23 @@ template <int GY>
 __host__ __device__ constexpr int tile_j()
 {
   return GY ? kTileJy : kTileJx;
+}
+
+// Tile width in columns used by a launch.  Defaults measured on B200 (tools/tile_sweep.py):
+// the one-shot plain kernels like small tiles when columns are independent (dim 0: 8, both
+// dims: 16) and long marches when they are not (dim 1: 128); the persistent fused kernels pay
+// a flag wait per boundary tile and like 32 (dim 0) / 128.  $GMT_TILE_JX / $GMT_TILE_JY
+// override (x-face flag chunks need kFlagCols % width == 0).
+inline int runtime_tile_j(int gx, int gy, bool fused)
+{
+  int dflt;
+  if (gy == 0) dflt = fused ? kTileJx : 8;
+  else if (gx == 0) dflt = kTileJy;
+  else dflt = fused ? kTileJy : 16;
+  const char* e = getenv(gy ? "GMT_TILE_JY" : "GMT_TILE_JX");
+  const int v = e ? atoi(e) : 0;
+  if (v < 4 || v > kStThreads || (kFlagCols % v) != 0) return dflt;
+  return v;
 }
 
 // four outputs from eight consecutive inputs: o_k = sten5(in[k..k+4]) * s
