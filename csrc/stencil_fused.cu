@@ -24,6 +24,7 @@
 
 #include "p2p.cuh"
 #include "stencil_tiles.cuh"
+#include "tma.cuh"
 
 namespace gmt {
 
@@ -168,7 +169,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
 // computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
 // each followed by its own fence + flag, so the exchange streams underneath the sweep: the
 // export front moves ~10x faster than the compute front.
-template <int GX, int GY, bool kDebug>
+template <int GX, int GY, bool kDebug, bool kNamedBar = false>
 __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i)
 {
   const int tid = threadIdx.x;
@@ -220,7 +221,10 @@ __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e,
         if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
       }
     }
-    __syncthreads();
+    if (kNamedBar)
+      asm volatile("bar.sync 1, %0;" ::"n"(kStThreads) : "memory");  // the 256 exporting threads only
+    else
+      __syncthreads();
     if (tid == 0) {
       fence_sys();
       if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
@@ -348,19 +352,123 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   finish_epoch(R.done, R.epoch, e, 2);
 }
 
+// ====================================================================== 2-D, dim-0 slabs
+// In the reference's dim-0 test (1024 x 524288 tile, halos = two strided 2 x 524288 strips)
+// EVERY tile touches both x faces, so the latency of "poll the chunk flag, fetch the ghost
+// pairs, put them into the array" would sit on the critical path of every tile.  Here it is
+// moved off it by warp specialisation: a ninth warp per CTA draws tiles from the shared
+// counter kDepth ahead of the compute warps, does the flag wait (ld.acquire.sys) and lands the
+// ghosts for each, then hands the tile over through an mbarrier ring.  The eight compute warps
+// never execute a CTA barrier in the loop: each waits on the ring slot, sweeps its rows of the
+// tile and releases the slot, so a fast warp can run ahead of a slow one.
+constexpr int kWsDepth = 2;
+
+template <bool kErr, bool kDebug>
+__global__ void __launch_bounds__(kStThreads + 32, 2)
+  fused_dim0_ws_kernel(const gmt_halo2d_rank* __restrict__ ranks, int TJ)
+{
+  __shared__ gmt_halo2d_rank R;
+  __shared__ double red[32];
+  __shared__ int64_t ring[kWsDepth];
+  __shared__ __align__(8) uint64_t full[kWsDepth];
+  __shared__ __align__(8) uint64_t empty[kWsDepth];
+  load_rank(R, ranks + blockIdx.y);
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int tid = threadIdx.x;
+  const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
+  const int64_t tiles_i = (nx + kTileI - 1) / kTileI, tiles_j = (ny + TJ - 1) / TJ;
+  const int64_t ntiles = tiles_i * tiles_j;
+  if (tid == 0) {
+    for (int s = 0; s < kWsDepth; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kStThreads / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  uint32_t* counter = R.done + 1;
+  double err = 0.0;
+
+  if (tid >= kStThreads) {
+    // ---------------- communication warp
+    const int lane = tid - kStThreads;
+    for (int k = 0;; ++k) {
+      const int slot = k % kWsDepth;
+      const uint32_t ph = (k / kWsDepth) & 1;
+      if (lane == 0) mbar_wait(&empty[slot], ph ^ 1);
+      __syncwarp();
+      long long t = 0;
+      if (lane == 0) t = (long long)atomicAdd(counter, 1u);
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (t >= ntiles) {
+        if (lane == 0) {
+          ring[slot] = -1;  // sentinel: the compute warps leave
+          mbar_arrive(&full[slot]);
+        }
+        break;
+      }
+      const int64_t tj = t / tiles_i, ti = t - tj * tiles_i;
+      const int64_t j0 = tj * TJ, j1 = min(ny, j0 + (int64_t)TJ);
+      const int sides = ((ti == 0 && R.has[0]) ? 1 : 0) | ((ti == tiles_i - 1 && R.has[1]) ? 2 : 0);
+      if (sides) {
+        if (lane < 2 && ((sides >> lane) & 1)) {
+          if (!wait_flag_ge(R.my_flag[lane] + j0 / kFlagCols, e, R.spin_limit)) atomicExch(R.status, 1u + lane);
+        }
+        __syncwarp();
+        for (int64_t j = j0 + lane; j < j1; j += 32) {
+          double* col = R.z + j * ldz;
+          if (sides & 1) stg128(col, ld_peer_f64x2(R.my_inbox[0][par] + 2 * j));
+          if (sides & 2) stg128(col + nx + 2, ld_peer_f64x2(R.my_inbox[1][par] + 2 * j));
+        }
+        __syncwarp();
+      }
+      if (lane == 0) {
+        ring[slot] = (int64_t)t;
+        mbar_arrive(&full[slot]);  // release: ring entry and landed ghosts are visible to the waiters
+      }
+    }
+  } else {
+    // ---------------- compute warps
+    push_faces<2, 0, kDebug, true>(R, e, par, tiles_i);
+    Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
+    for (int k = 0;; ++k) {
+      const int slot = k % kWsDepth;
+      const uint32_t ph = (k / kWsDepth) & 1;
+      mbar_wait(&full[slot], ph);
+      const int64_t t = ring[slot];
+      if (t < 0) break;
+      const int64_t tj = t / tiles_i, ti = t - tj * tiles_i;
+      const int64_t j0 = tj * TJ;
+      tile2d<2, 0, kErr>(S, ti * kTileI, j0, min(ny, j0 + (int64_t)TJ), tid, err);
+      __syncwarp();
+      if ((tid & 31) == 0) mbar_arrive(&empty[slot]);
+    }
+  }
+  __syncthreads();
+  if (kErr) {
+    const double part = block_sum(err, red);
+    double total;
+    if (grid_sum_last_block(part, R.err_scratch, red, total, gridDim.x, blockIdx.x)) {
+      if (tid == 0) *R.err_sumsq = total;
+    }
+  }
+  finish_epoch(R.done, R.epoch, e, 2);
+}
+
 template <typename RankT>
 static int launch_fused(const void* kernel, const RankT* ranks_dev, int n_ranks, int64_t ntiles,
-                        cudaStream_t st, int tile_j_arg = 0)
+                        cudaStream_t st, int tile_j_arg = 0, int threads = kStThreads)
 {
   int grid = 0;
-  int rc = persistent_grid(kernel, kStThreads, ntiles, n_ranks, &grid);
+  int rc = persistent_grid(kernel, threads, ntiles, n_ranks, &grid);
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&tile_j_arg};
   if (n_ranks > 1) {
     // several ranks spin on one another inside one launch: co-residency must be guaranteed
-    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(kStThreads), args, 0, st));
+    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(threads), args, 0, st));
   } else {
-    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(kStThreads), args, 0, st));
+    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(threads), args, 0, st));
   }
   return 0;
 }
@@ -397,8 +505,11 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
 #define GMT_PICK(GX_, GY_)                                                                                   \
   (dbg ? (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, true> : (const void*)fused2d_kernel<GX_, GY_, false, true>) \
        : (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, false> : (const void*)fused2d_kernel<GX_, GY_, false, false>))
+  int threads = kStThreads;
   if (gx && !gy) {
-    k = GMT_PICK(2, 0);
+    k = dbg ? (with_err ? (const void*)fused_dim0_ws_kernel<true, true> : (const void*)fused_dim0_ws_kernel<false, true>)
+            : (with_err ? (const void*)fused_dim0_ws_kernel<true, false> : (const void*)fused_dim0_ws_kernel<false, false>);
+    threads = kStThreads + 32;
     nt = tiles_i * ((ny + tj - 1) / tj);
   } else if (!gx && gy) {
     k = GMT_PICK(0, 2);
@@ -408,7 +519,7 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
     nt = tiles_i * ((ny + tj - 1) / tj);
   }
 #undef GMT_PICK
-  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj);
+  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj, threads);
 }
 
 int gmt_debug_set_push_delay(unsigned int max_ns)

@@ -31,14 +31,14 @@ __host__ __device__ constexpr int tile_j()
 }
 
 // Tile width in columns used by a launch.  Defaults measured on B200 (tools/tile_sweep.py):
-// the one-shot plain kernels like small tiles when columns are independent (dim 0: 8, both
-// dims: 16) and long marches when they are not (dim 1: 128); the persistent fused kernels pay
-// a flag wait per boundary tile and like 32 (dim 0) / 128.  $GMT_TILE_JX / $GMT_TILE_JY
+// small tiles when columns are independent (dim 0: 8 columns = 128 KB of traffic, for the plain
+// and the warp-specialised fused kernel alike), 16 for the plain both-dims kernel, long marches
+// when columns are coupled (dim 1 and the fused both-dims kernel: 128).  $GMT_TILE_JX / $GMT_TILE_JY
 // override (x-face flag chunks need kFlagCols % width == 0).
 inline int runtime_tile_j(int gx, int gy, bool fused)
 {
   int dflt;
-  if (gy == 0) dflt = fused ? kTileJx : 8;
+  if (gy == 0) dflt = 8;
   else if (gx == 0) dflt = kTileJy;
   else dflt = fused ? kTileJy : 16;
   const char* e = getenv(gy ? "GMT_TILE_JY" : "GMT_TILE_JX");
