@@ -86,8 +86,16 @@ def main() -> int:
     glups = points / (t["ms_per_step"] * 1e-3) / 1e9
 
     # ---- end to end through the public API: H2D boundary values + step + D2H error norm
-    h2d, d2h = wl.e2e_bytes()
-    te = timing.time_steps(wl.step_e2e, args.steps, warmup, rt.device)
+    # (host_fed plan: the boundary upload goes straight into the kernel's inbox on a side stream and
+    # overlaps the interior sweep -- the host is treated as one more neighbour)
+    wl_e = Stencil2DWorkload(rt, n, n, mode="grid", impl=args.impl, with_err=True, host_fed=(args.impl == "fused"))
+    wl_e.setup()
+    h2d, d2h = wl_e.e2e_bytes()
+    te = timing.time_steps(wl_e.step_e2e, args.steps, warmup, rt.device)
+    wl_e.check()
+    err_e = max(wl_e.err_norm(r) for r in wl_e.ranks)
+    del wl_e
+    torch.cuda.empty_cache()
     e2e_glups = points / (te["ms_per_step"] * 1e-3) / 1e9
     # a 20-step region lasts ~15 ms, shorter than nvidia-smi's sampling period: keep the same
     # kernel running (untimed) until the sampler has seen the GPU under load a few times
@@ -141,7 +149,7 @@ def main() -> int:
         "gpu_launches": args.steps * wl.launches_per_step,
         "roofline": {"hbm_gbs_per_gpu": per_gpu_gbs, "frac_of_measured_copy_peak": per_gpu_gbs / hbm,
                      "measured_copy_peak_gbs": hbm},
-        "err_norm_max": max(err0, err1),
+        "err_norm_max": max(err0, err1, err_e),
         "extra": extra,
     }
     if rt.rank == 0:

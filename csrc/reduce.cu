@@ -161,6 +161,12 @@ __global__ void __launch_bounds__(512) fill_kernel(int64_t n, double v, double* 
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) x[i] = v;
 }
 
+__global__ void __launch_bounds__(256) fill_u64_kernel(int64_t n, uint64_t v, uint64_t* x)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) x[i] = v;
+}
+
 __global__ void __launch_bounds__(512)
   iota_kernel(int64_t n, double start, double step, double mul, double* x)
 {
@@ -271,6 +277,15 @@ int gmt_fill_f64(int64_t n, double value, double* x, gmt_stream_t stream)
   GMT_REQUIRE(n >= 0 && (n == 0 || x), GMT_EINVAL, "gmt_fill_f64: bad argument");
   if (n == 0) return 0;
   gmt::fill_kernel<<<gmt::grid_for(n, 512, 4), 512, 0, gmt::as_stream(stream)>>>(n, value, x);
+  GMT_LAUNCH_CHECK();
+  return 0;
+}
+
+int gmt_fill_u64(int64_t n, uint64_t value, uint64_t* x, gmt_stream_t stream)
+{
+  GMT_REQUIRE(n >= 0 && (n == 0 || x), GMT_EINVAL, "gmt_fill_u64: bad argument");
+  if (n == 0) return 0;
+  gmt::fill_u64_kernel<<<gmt::grid_for(n, 256, 1), 256, 0, gmt::as_stream(stream)>>>(n, value, x);
   GMT_LAUNCH_CHECK();
   return 0;
 }

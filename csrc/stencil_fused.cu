@@ -190,7 +190,7 @@ __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e,
       side = 2 + (int)((u - 2 * nfx) & 1);
       c = (u - 2 * nfx) >> 1;
     }
-    if (!R.has[side]) continue;  // CTA-uniform
+    if (R.has[side] != 1) continue;  // CTA-uniform; 2 = fed by the host, nothing to export
     double* box = R.peer_inbox[side][par];
     if (side < 2) {
       const int64_t j0 = c * kFlagCols;
@@ -456,6 +456,17 @@ __global__ void __launch_bounds__(kStThreads + 32, 2)
   finish_epoch(R.done, R.epoch, e, 2);
 }
 
+// flags[i] <- *epoch + 1 with release semantics: "the host-fed ghost values of the step now
+// running are in the inbox".  Runs on the stream that carried the host-to-device copy, next to
+// the fused kernel of that step (which bumps *epoch only when it finishes, i.e. after it has
+// seen these flags).
+__global__ void publish_flags_kernel(uint64_t* flags, int64_t n, const uint64_t* epoch)
+{
+  const uint64_t e = ld_relaxed_sys(epoch) + 1;
+  __threadfence_system();
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) st_release_sys(flags + i, e);
+}
+
 template <typename RankT>
 static int launch_fused(const void* kernel, const RankT* ranks_dev, int n_ranks, int64_t ntiles,
                         cudaStream_t st, int tile_j_arg = 0, int threads = kStThreads)
@@ -520,6 +531,15 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   }
 #undef GMT_PICK
   return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj, threads);
+}
+
+int gmt_publish_epoch_flags(uint64_t* flags, int64_t n, const uint64_t* epoch, gmt_stream_t stream)
+{
+  GMT_REQUIRE(flags && epoch && n >= 0, GMT_EINVAL, "gmt_publish_epoch_flags: bad argument");
+  if (n == 0) return 0;
+  gmt::publish_flags_kernel<<<1, 256, 0, gmt::as_stream(stream)>>>(flags, n, epoch);
+  GMT_LAUNCH_CHECK();
+  return 0;
 }
 
 int gmt_debug_set_push_delay(unsigned int max_ns)

@@ -18,7 +18,10 @@ namespace gmt {
 
 constexpr int kStThreads = 256;           // threads per CTA
 constexpr int kTileI = kStThreads * 4;    // points of the contiguous axis per tile
-constexpr int kBatch = 4;                 // columns (or sub-blocks) loaded per batch
+#ifndef GMT_KBATCH
+#define GMT_KBATCH 4
+#endif
+constexpr int kBatch = GMT_KBATCH;        // columns (or sub-blocks) loaded per batch
 constexpr int kTile1d = kTileI * kBatch;  // 1-D tile: 4096 points
 constexpr int kTileJx = 32;               // columns per tile when only dim 0 is differentiated
 constexpr int kTileJy = 128;              // columns per tile when dim 1 is differentiated

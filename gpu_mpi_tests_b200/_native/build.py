@@ -46,7 +46,8 @@ def _headers_mtime() -> float:
 
 
 def _compile(nvcc: str, src: Path, obj: Path, verbose: bool) -> str:
-    cmd = [nvcc, *NVCC_FLAGS, "-I", str(ROOT / "include"), "-c", str(src), "-o", str(obj)]
+    extra = os.environ.get("GMT_NVCC_EXTRA", "").split()
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", str(ROOT / "include"), "-c", str(src), "-o", str(obj)]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"nvcc failed for {src.name}:\n{res.stdout}\n{res.stderr}")

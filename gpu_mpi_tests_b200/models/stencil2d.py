@@ -31,7 +31,7 @@ class Stencil2DWorkload:
     def __init__(self, rt: "_rt.Runtime | None" = None, nx: int = 16384, ny: int = 16384, mode: str = "grid",
                  impl: str = "fused", with_err: bool = True, space: PeerSpace | None = None,
                  grid: tuple | None = None, stage: str = "none", mem_space: str = "device",
-                 spin_limit: int = 0):
+                 spin_limit: int = 0, host_fed: bool = False):
         """mode: 'grid' (gx=gy=2, px x py ranks), 'dim0' (gx=2, world x 1), 'dim1' (gy=2, 1 x world).
         nx, ny: per-rank interior extents (weak scaling)."""
         self.rt = rt or _rt.current()
@@ -55,7 +55,7 @@ class Stencil2DWorkload:
                 raise RuntimeError("impl='fused' needs CUDA; use impl='baseline' on the CPU/gloo path")
             self.space = space if space is not None else make_space(self.rt)
             self.plan = FusedStencil2D(self.space, self.px, self.py, nx, ny, self.gx, self.gy, with_err=with_err,
-                                       spin_limit=spin_limit, mem_space=mem_space)
+                                       spin_limit=spin_limit, mem_space=mem_space, host_fed=host_fed)
             self.ranks = self.plan.ranks
             self.z, self.out = self.plan.z, self.plan.out
             self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy
@@ -70,12 +70,21 @@ class Stencil2DWorkload:
         else:
             raise ValueError("impl must be fused or baseline")
         self._host_bc = None
+        self.host_fed = bool(host_fed) and impl == "fused"
 
     # ------------------------------------------------------------------ setup / step
     def setup(self, poison: float = 0.0) -> None:
         self.plan.init_analytic(poison=poison)
+        if self.host_fed:
+            # the kernel takes the host-fed ghosts from its inbox: start it off with the analytic values
+            for (r, side), (off, cnt, _f) in self.plan.host_sides.items():
+                self.plan.hostbox[r][off:off + cnt].view(self.plan.host_side_shape(side)).copy_(
+                    self.plan.ghost_view(r, side))
 
     def step(self) -> None:
+        if self.host_fed:
+            for r in self.ranks:  # no new host data this step: re-announce what the inbox holds
+                self.plan.publish_host_sides(r)
         self.plan.step()
 
     def points_per_rank(self) -> int:
@@ -86,10 +95,38 @@ class Stencil2DWorkload:
         return 16 * self.nx * self.ny
 
     # ------------------------------------------------------------------ end to end
+    def _prepare_e2e_host_fed(self) -> None:
+        """host_fed plans: a pinned buffer per hosted rank mirrors plan.hostbox (the kernel's inbox
+        for the host-fed sides), so ONE H2D copy delivers all sides and no scatter kernel is needed."""
+        plan = self.plan
+        self._bc_views = {}
+        self._fed = []   # (pinned host buffer, device inbox) per hosted rank that has host-fed sides
+        total = 0
+        for r in self.ranks:
+            box = plan.hostbox.get(r)
+            if box is None:
+                continue
+            h = torch.empty(box.numel(), dtype=F64, pin_memory=True)
+            for (rr, side), (off, cnt, _f) in plan.host_sides.items():
+                if rr == r:
+                    # inbox layouts: x faces [2*j + r] == row-major (ny, 2); y faces [r*nx + i] == (2, nx)
+                    h[off:off + cnt].view(plan.host_side_shape(side)).copy_(plan.ghost_view(rr, side))
+            self._fed.append((h, box))
+            total += box.numel()
+        self._bc_total = total
+        self._host_bc = self._fed[0][0] if self._fed else torch.empty(1, dtype=F64, pin_memory=True)
+        self._err_dev = torch.zeros(len(self.ranks), dtype=F64, device=self.device)
+        self._err_host = torch.zeros(len(self.ranks), dtype=F64, pin_memory=True)
+        self._graph = None
+        self._graph_failed = False
+        self._side_stream = torch.cuda.Stream(device=self.device)
+
     def _prepare_e2e(self) -> None:
         """Per-step host input and output: ONE pinned buffer holding this rank's physical-boundary
         ghost values (all sides back to back), its device staging twin, and a pinned scalar for the
         per-step result."""
+        if self.host_fed:
+            return self._prepare_e2e_host_fed()
         pin = self.device.type == "cuda"
         self._bc_views = {}
         total = 0
@@ -127,6 +164,25 @@ class Stencil2DWorkload:
 
     def _e2e_body(self) -> None:
         """Stream-ordered body of one end-to-end step (also what gets captured in a CUDA graph)."""
+        if self.host_fed:
+            # two branches: the fused kernel starts at once on the main stream and sweeps the
+            # interior, while the side stream uploads the boundary values straight into the kernel's
+            # inbox and then publishes their flags; the kernel's boundary tiles (processed last) pick
+            # them up like a neighbour's.  The upload is hidden behind ~95% of the sweep.
+            main = torch.cuda.current_stream()
+            side = self._side_stream
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                for h, box in self._fed:
+                    box.copy_(h, non_blocking=True)
+                for r in self.ranks:
+                    self.plan.publish_host_sides(r)
+            self.plan.step()
+            main.wait_stream(side)
+            for k, r in enumerate(self.ranks):
+                self._err_dev[k:k + 1].copy_(self.err_sumsq(r))
+            self._err_host.copy_(self._err_dev, non_blocking=True)
+            return
         if self._bc_total:
             self._dev_bc.copy_(self._host_bc, non_blocking=True)          # one H2D for all sides
             for (r, side), (off, v) in self._bc_views.items():

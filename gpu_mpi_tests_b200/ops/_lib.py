@@ -119,6 +119,7 @@ _SIGS = {
     "gmt_sumsq_diff2d_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr]),
     "gmt_axis_sum_f64": (None, [c_i64, c_i64, c_i64, c_ptr, C.c_int, c_i64, c_ptr, c_ptr]),
     "gmt_fill_f64": (None, [c_i64, c_dbl, c_ptr, c_ptr]),
+    "gmt_fill_u64": (None, [c_i64, C.c_uint64, c_ptr, c_ptr]),
     "gmt_iota_f64": (None, [c_i64, c_dbl, c_dbl, c_dbl, c_ptr, c_ptr]),
     "gmt_stencil1d_f64": (None, [c_i64, c_ptr, c_ptr, c_dbl, C.c_int, c_ptr]),
     "gmt_stencil2d_f64": (None, [C.c_int, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, C.c_int, c_ptr]),
@@ -132,6 +133,7 @@ _SIGS = {
     "gmt_fused_stencil2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, C.c_int, c_ptr]),
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),
     "gmt_debug_set_push_delay": (None, [C.c_uint]),
+    "gmt_publish_epoch_flags": (None, [c_ptr, c_i64, c_ptr, c_ptr]),
     "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_gather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),

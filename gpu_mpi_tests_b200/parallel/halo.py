@@ -135,7 +135,7 @@ class FusedStencil2D(_PlanBase):
 
     def __init__(self, space: PeerSpace, px: int, py: int, nx: int, ny: int, gx: int = 2, gy: int = 2,
                  with_err: bool = True, spin_limit: int = 0, dx: float | None = None, dy: float | None = None,
-                 wx: float = 1.0, wy: float = 1.0, mem_space: str = "device"):
+                 wx: float = 1.0, wy: float = 1.0, mem_space: str = "device", host_fed: bool = False):
         super().__init__(space, with_err, spin_limit)
         if px * py != space.world:
             raise ValueError(f"grid {px}x{py} does not match world {space.world}")
@@ -168,6 +168,12 @@ class FusedStencil2D(_PlanBase):
                 self.off_inbox[side][p] = self.heap.take(box_x if side < 2 else box_y)
             self.off_flag[side] = self.heap.take((nfx if side < 2 else nfy) * 8)
         buf = self.heap.buf
+        # host-fed physical sides ("the host is one more neighbour"): their ghost values arrive by
+        # a host-to-device copy into a local inbox while the kernel is already sweeping the interior
+        self.host_fed = bool(host_fed)
+        self.host_sides = {}     # (rank, side) -> (offset in doubles into hostbox[rank], count, flag tensor)
+        self.hostbox = {}
+        self._hostflags = {}
         structs = []
         for r in self.ranks:
             k = self._slot(r)
@@ -175,6 +181,12 @@ class FusedStencil2D(_PlanBase):
             s = Halo2dRank()
             s.z, s.out = self.z[r].data_ptr(), self.out[r].data_ptr()
             s.nx, s.ny, s.ldz, s.ldo, s.gx, s.gy, s.sx, s.sy = nx, ny, self.ldz, nx, gx, gy, self.sx, self.sy
+            fed = [side for side in range(4) if (gx if side < 2 else gy) and g.neighbour(side) < 0] if host_fed else []
+            total = sum(2 * (ny if side < 2 else nx) for side in fed)
+            if fed:
+                self.hostbox[r] = torch.zeros(total, dtype=F64, device=self.device)
+                self._hostflags[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, device=self.device)
+            off = 0
             for side in range(4):
                 used = gx if side < 2 else gy
                 nb = g.neighbour(side) if used else -1
@@ -185,6 +197,16 @@ class FusedStencil2D(_PlanBase):
                     s.peer_inbox[side][p] = buf.ptr(nb, self.off_inbox[opp][p]) if nb >= 0 else 0
                 s.my_flag[side] = buf.ptr(r, self.off_flag[side]) if used else 0
                 s.peer_flag[side] = buf.ptr(nb, self.off_flag[opp]) if nb >= 0 else 0
+                if side in fed:
+                    cnt = 2 * (ny if side < 2 else nx)
+                    s.has[side] = 2
+                    box = self.hostbox[r][off:off + cnt]
+                    # one buffer for both parities: host feeds are stream-ordered between steps
+                    s.my_inbox[side][0] = s.my_inbox[side][1] = box.data_ptr()
+                    nflags = nfx if side < 2 else nfy
+                    s.my_flag[side] = self._hostflags[r][side].data_ptr()
+                    self.host_sides[(r, side)] = (off, cnt, self._hostflags[r][side][:nflags])
+                    off += cnt
             s.epoch, s.done, s.status = (self._epoch[k].data_ptr(), self._done[k].data_ptr(),
                                          self._status[k].data_ptr())
             s.err_scratch, s.err_sumsq = self._scratch[k].data_ptr(), self._errs[k].data_ptr()
@@ -222,6 +244,27 @@ class FusedStencil2D(_PlanBase):
         lib.gmt_fused_stencil2d_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.nx, self.ny, self.gx, self.gy,
                                     int(self.with_err), torch.cuda.current_stream().cuda_stream)
         self.steps += 1
+
+    # ---- host-fed sides ------------------------------------------------------------------
+    def host_side_shape(self, side: int) -> tuple:
+        """Shape of the host tensor feeding `side`: x faces (ny, 2) [2 ghost rows per column],
+        y faces (2, nx) [2 ghost columns]."""
+        return (self.ny, 2) if side < 2 else (2, self.nx)
+
+    def ghost_view(self, rank: int, side: int) -> torch.Tensor:
+        """The array's own ghost cells of a side as a strided view with host_side_shape."""
+        z, gx, gy, nx, ny = self.z[rank], self.gx, self.gy, self.nx, self.ny
+        return [z[gy:gy + ny, 0:2], z[gy:gy + ny, gx + nx:gx + nx + 2], z[0:2, gx:gx + nx],
+                z[gy + ny:gy + ny + 2, gx:gx + nx]][side]
+
+    def publish_host_sides(self, rank: int) -> None:
+        """After the host-to-device copy into hostbox[rank] (same stream): mark the host-fed sides of
+        the step that is running / about to run as arrived."""
+        k = self._slot(rank)
+        st = torch.cuda.current_stream().cuda_stream
+        for (r, side), (_off, _cnt, flags) in self.host_sides.items():
+            if r == rank:
+                lib.gmt_publish_epoch_flags(flags.data_ptr(), flags.numel(), self._epoch[k].data_ptr(), st)
 
     def halo_bytes_out(self, rank: int) -> int:
         """Bytes this rank stores into neighbours' inboxes per step."""

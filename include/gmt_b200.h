@@ -134,6 +134,8 @@ int gmt_axis_sum_f64(int64_t nx, int64_t ny, int64_t ld, const double* z, int ax
                      double* out, gmt_stream_t stream);
 /* x[:] <- value  (fill ctor mpi_stencil2d_gt.cc:598) */
 int gmt_fill_f64(int64_t n, double value, double* x, gmt_stream_t stream);
+/* x[:] <- value for 64-bit words (epoch flags set from a stream) */
+int gmt_fill_u64(int64_t n, uint64_t value, uint64_t* x, gmt_stream_t stream);
 /* x[i] <- (start + i*step)*mul   -- daxpy initialisers (mpi_daxpy_nvtx.cc:209-212) */
 int gmt_iota_f64(int64_t n, double start, double step, double mul, double* x, gmt_stream_t stream);
 
@@ -236,7 +238,11 @@ typedef struct {
   int64_t nx, ny, ldz, ldo;
   int32_t gx, gy;
   double sx, sy;
-  int32_t has[4];
+  int32_t has[4];           /* 0: physical boundary (ghosts used as they are); 1: neighbour rank (export my
+                               boundary to it, wait for its flags); 2: ghosts are FED BY THE HOST for this
+                               step -- nothing is exported, the side's tiles wait for my_flag like for a
+                               neighbour (the caller copies the values into my_inbox[side][e & 1] and then
+                               sets the side's flag words to e, e.g. from a copy stream) */
   double* my_inbox[4][2];
   double* peer_inbox[4][2];
   uint64_t* my_flag[4];     /* gmt_halo2d_flag_count(side, nx, ny) words per side */
@@ -252,6 +258,10 @@ typedef struct {
 
 int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
                             int gx, int gy, int with_err, gmt_stream_t stream);
+/* For sides with has == 2: after the host-to-device copy of the ghost values into my_inbox, publish
+ * "arrived" for the step that is currently running / about to run: flags[i] <- *epoch + 1 (release).
+ * Call it on the stream that carried the copy; it may run concurrently with that step's kernel. */
+int gmt_publish_epoch_flags(uint64_t* flags, int64_t n, const uint64_t* epoch, gmt_stream_t stream);
 /* Test hook: sleep a pseudo-random time of up to max_ns nanoseconds before every halo flag
  * store (0 = off, the default).  Shakes the flag/epoch/parity protocol in stress tests.   */
 int gmt_debug_set_push_delay(unsigned int max_ns);

@@ -125,3 +125,46 @@ def test_dead_neighbour_times_out_instead_of_hanging(dev):
     torch.cuda.synchronize()
     with pytest.raises(HaloTimeout):
         plan.check_status()
+
+
+@pytest.mark.parametrize("px,py", [(1, 1), (2, 2)])
+def test_host_fed_sides_behave_like_a_neighbour(dev, px, py):
+    """Physical-boundary ghosts delivered by the host while the kernel is already running
+    (has == 2): same result as ghosts that were in the array beforehand, and new host values
+    show up in the array's ghost cells after the step."""
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.parallel import runtime
+    rt = runtime.init()
+    nx, ny = 2048, 384
+    ref = Stencil2DWorkload(rt, nx, ny, mode="grid", impl="fused", space=VirtualSpace(px * py, dev), grid=(px, py),
+                            spin_limit=1 << 26)
+    fed = Stencil2DWorkload(rt, nx, ny, mode="grid", impl="fused", space=VirtualSpace(px * py, dev), grid=(px, py),
+                            spin_limit=1 << 26, host_fed=True)
+    ref.setup()
+    fed.setup(poison=0.0)
+    for r in fed.ranks:  # the in-array physical ghosts must NOT be what makes the result right
+        for (rr, side) in fed.plan.host_sides:
+            if rr == r:
+                fed.plan.ghost_view(r, side).fill_(1e30)
+    for _ in range(3):
+        ref.step()
+        fed.step()
+    e_ref = ref.step_e2e()
+    e_fed = fed.step_e2e()
+    e_fed = fed.step_e2e()  # second call replays the captured graph (single hosted rank) or re-runs eagerly
+    torch.cuda.synchronize()
+    fed.check()
+    assert e_fed == pytest.approx(e_ref, rel=1e-6, abs=1e-9)
+    for r in fed.ranks:
+        assert close(fed.out[r], ref.out[r])
+        for (rr, side) in fed.plan.host_sides:
+            if rr == r:  # the kernel landed the host values in the array's own ghost cells
+                assert torch.equal(fed.plan.ghost_view(r, side), ref.plan.ghost_view(r, side))
+    # new boundary values from the host reach the array
+    for h, _box in fed._fed:
+        h.add_(1.0)
+    fed.step_e2e()
+    torch.cuda.synchronize()
+    r0 = fed.ranks[0]
+    side0 = [s for (rr, s) in fed.plan.host_sides if rr == r0][0]
+    assert torch.allclose(fed.plan.ghost_view(r0, side0), ref.plan.ghost_view(r0, side0) + 1.0)
