@@ -232,3 +232,30 @@ def test_golden_output_strings():
     assert report.mpi_error("f.cc", 35, 13) == "f.cc:35 error 13"
     assert "MEMORY_PER_CORE=" in report.mpienv_line(3, 4096)
     assert report.sycl_banner(2, 0, 524288, 2048, 1024, 100, 5, False)[-1] == "stage_host = 0"
+
+
+def test_dist_arrays_world_of_one_cpu(monkeypatch):
+    """The user-facing distributed-array objects on the CPU path (world of one)."""
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    from gpu_mpi_tests_b200.parallel.darray import DistArray1D, DistArray2D
+    rt = runtime.init(use_cuda=False)
+    a = DistArray1D(rt, 1 << 12)
+    a.fill_analytic()
+    a.exchange()
+    d = a.derivative()
+    assert d.shape == (1 << 12,) and a.err_norm() < 1e-6
+    assert a.interior.shape == (1 << 12,) and a.local.shape == ((1 << 12) + 4,)
+    for dims, ghosts in (((0,), (2, 0)), ((1,), (0, 2)), ((0, 1), (2, 2))):
+        b = DistArray2D(rt, 64, 48, dims=dims)
+        assert (b.gx, b.gy) == ghosts
+        b.fill_analytic()
+        b.exchange()
+        out = b.derivative()
+        assert out.shape == (48, 64) and b.err_norm() < 1e-8
+        assert b.interior.shape == (48, 64)
+        if 0 in dims:
+            assert b.ghost(0).shape == (48, 2)
+        if 1 in dims:
+            assert b.ghost(3).shape == (2, 64)
+    runtime.finalize()
