@@ -269,7 +269,17 @@ __device__ __forceinline__ void decode_tile(const TileMap& M, int64_t c, int64_t
   }
 }
 
-template <int GX, int GY, bool kErr, bool kDebug>
+// kOneShot = false: persistent grid, tiles drawn from a counter -- needed when several virtual
+//   ranks share one cooperative launch (every CTA must be resident for the spin-waits to be safe).
+// kOneShot = true: one tile per CTA in blockIdx order (the plain kernels' fastest pattern);
+//   opt-in (GMT_FUSED_ONESHOT=1) for launches that hold ONE rank.  Measured SLOWER than the
+//   persistent mode for this kernel (16384^2: 0.779 vs 0.669 ms; dim 0: 1.388 vs 1.26 ms) -- the
+//   interior-first tile order breaks the in-order front that makes one-shot grids fast, and the
+//   per-CTA prologue (descriptor load, epoch read) is paid per tile.  Safe without
+//   co-residency: the exporting CTAs are the lowest block indices, hence scheduled first, and
+//   never wait; the CTAs that wait (boundary tiles, highest indices) wait only for ANOTHER GPU's
+//   exporting CTAs, never for a later CTA of their own grid.
+template <int GX, int GY, bool kErr, bool kDebug, bool kOneShot>
 __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d_rank* __restrict__ ranks, int TJ)
 {
   __shared__ gmt_halo2d_rank R;
@@ -300,11 +310,17 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   double err = 0.0;
   // (no prefetched draw here, unlike the 1-D kernel: 2-D tiles are 0.5-2 MB, the atomic's
   // latency is noise, and a tile pre-claimed by a still-busy CTA would lengthen the tail)
-  for (;;) {
-    __syncthreads();
-    if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
-    __syncthreads();
-    const int64_t c = next_tile[0];
+  for (int trip = 0;; ++trip) {
+    int64_t c;
+    if (kOneShot) {
+      if (trip > 0) break;
+      c = blockIdx.x;
+    } else {
+      __syncthreads();
+      if (tid == 0) next_tile[0] = (int64_t)atomicAdd(counter, 1u);
+      __syncthreads();
+      c = next_tile[0];
+    }
     if (c >= ntiles) break;
     int64_t ti, tj;
     decode_tile(M, c, ti, tj);
@@ -342,12 +358,38 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
     }
     tile2d<GX, GY, kErr>(S, i0, j0, j1, tid, err);
   }
-  if (kErr) {
+  if (kErr && !kOneShot) {
     const double part = block_sum(err, red);
     double total;
     if (grid_sum_last_block(part, R.err_scratch, red, total, gridDim.x, blockIdx.x)) {
       if (tid == 0) *R.err_sumsq = total;
     }
+  }
+  if (kOneShot) {
+    // thousands of CTAs: their partials go into an accumulator (two of them, used by alternating
+    // steps, so the one for the next step can be cleared while this one is still being read)
+    double* acc = reinterpret_cast<double*>(reinterpret_cast<char*>(R.err_scratch) + kScratchHeaderBytes);
+    if (kErr) {
+      const double part = block_sum(err, red);
+      if (tid == 0) atomicAdd(acc + par, part);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      const unsigned int t = atomicAdd(R.done, 1u);
+      if (t == gridDim.x - 1) {
+        __threadfence();
+        if (kErr) {
+          *R.err_sumsq = __ldcg(acc + par);
+          acc[par ^ 1] = 0.0;
+        }
+        R.done[0] = 0u;
+        R.done[1] = 0u;
+        __threadfence();
+        st_relaxed_sys(R.epoch, e);
+      }
+    }
+    return;
   }
   finish_epoch(R.done, R.epoch, e, 2);
 }
@@ -469,11 +511,16 @@ __global__ void publish_flags_kernel(uint64_t* flags, int64_t n, const uint64_t*
 
 template <typename RankT>
 static int launch_fused(const void* kernel, const RankT* ranks_dev, int n_ranks, int64_t ntiles,
-                        cudaStream_t st, int tile_j_arg = 0, int threads = kStThreads)
+                        cudaStream_t st, int tile_j_arg = 0, int threads = kStThreads, bool oneshot = false)
 {
   int grid = 0;
-  int rc = persistent_grid(kernel, threads, ntiles, n_ranks, &grid);
-  if (rc) return rc;
+  if (oneshot) {
+    GMT_REQUIRE(ntiles < (1LL << 31), GMT_ETOOBIG, "fused stencil: array too large for a one-shot grid");
+    grid = (int)std::max<int64_t>(1, ntiles);
+  } else {
+    int rc = persistent_grid(kernel, threads, ntiles, n_ranks, &grid);
+    if (rc) return rc;
+  }
   void* args[] = {(void*)&ranks_dev, (void*)&tile_j_arg};
   if (n_ranks > 1) {
     // several ranks spin on one another inside one launch: co-residency must be guaranteed
@@ -510,14 +557,21 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   GMT_REQUIRE(nx % 4 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil2d_f64: nx must be a multiple of 4");
   const void* k = nullptr;
   const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
-  const int tj = runtime_tile_j(gx, gy, true);
+  // one rank per launch (production): one-shot grid with the plain kernels' tile widths
+  const char* os_env = getenv("GMT_FUSED_ONESHOT");
+  const bool oneshot = n_ranks == 1 && os_env && os_env[0] == '1';  // opt-in: measured slower (0.779 vs 0.669 ms)
+  const int tj = runtime_tile_j(gx, gy, !oneshot);
   int64_t nt = 0;
   const bool dbg = g_debug_push_delay_host != 0;
-#define GMT_PICK(GX_, GY_)                                                                                   \
-  (dbg ? (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, true> : (const void*)fused2d_kernel<GX_, GY_, false, true>) \
-       : (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, false> : (const void*)fused2d_kernel<GX_, GY_, false, false>))
+#define GMT_PICK1(GX_, GY_, OS_)                                                                             \
+  (dbg ? (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, true, OS_> : (const void*)fused2d_kernel<GX_, GY_, false, true, OS_>) \
+       : (with_err ? (const void*)fused2d_kernel<GX_, GY_, true, false, OS_> : (const void*)fused2d_kernel<GX_, GY_, false, false, OS_>))
+#define GMT_PICK(GX_, GY_) (oneshot ? GMT_PICK1(GX_, GY_, true) : GMT_PICK1(GX_, GY_, false))
   int threads = kStThreads;
-  if (gx && !gy) {
+  if (gx && !gy && oneshot) {
+    k = GMT_PICK(2, 0);
+    nt = tiles_i * ((ny + tj - 1) / tj);
+  } else if (gx && !gy) {
     k = dbg ? (with_err ? (const void*)fused_dim0_ws_kernel<true, true> : (const void*)fused_dim0_ws_kernel<false, true>)
             : (with_err ? (const void*)fused_dim0_ws_kernel<true, false> : (const void*)fused_dim0_ws_kernel<false, false>);
     threads = kStThreads + 32;
@@ -530,7 +584,8 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
     nt = tiles_i * ((ny + tj - 1) / tj);
   }
 #undef GMT_PICK
-  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj, threads);
+#undef GMT_PICK1
+  return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj, threads, oneshot);
 }
 
 int gmt_publish_epoch_flags(uint64_t* flags, int64_t n, const uint64_t* epoch, gmt_stream_t stream)

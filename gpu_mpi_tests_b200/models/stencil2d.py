@@ -176,7 +176,7 @@ class Stencil2DWorkload:
                 for h, box in self._fed:
                     box.copy_(h, non_blocking=True)
                 for r in self.ranks:
-                    self.plan.publish_host_sides(r)
+                    self.plan.publish_host_sides_by_copy(r)   # copy engine: needs no SM slot
             self.plan.step()
             main.wait_stream(side)
             for k, r in enumerate(self.ranks):
@@ -208,15 +208,20 @@ class Stencil2DWorkload:
                 self._e2e_body()                      # warm-up outside capture
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
+                steps_before = self.plan.steps
                 with torch.cuda.graph(g):
                     self._e2e_body()
+                self.plan.steps = steps_before   # capture launched nothing: the device epoch did not move
                 self._graph = g
             except Exception:  # noqa: BLE001 - capture is an optimisation, never a requirement
                 self._graph_failed = True
                 self._graph = None
                 torch.cuda.synchronize(self.device)
         if graphable and self._graph is not None:
+            if self.host_fed:
+                self.plan.refresh_host_epoch()
             self._graph.replay()
+            self.plan.steps += 1
         else:
             self._e2e_body()
         if cuda:

@@ -174,6 +174,7 @@ class FusedStencil2D(_PlanBase):
         self.host_sides = {}     # (rank, side) -> (offset in doubles into hostbox[rank], count, flag tensor)
         self.hostbox = {}
         self._hostflags = {}
+        self._hostflags_pinned = {}
         structs = []
         for r in self.ranks:
             k = self._slot(r)
@@ -186,6 +187,7 @@ class FusedStencil2D(_PlanBase):
             if fed:
                 self.hostbox[r] = torch.zeros(total, dtype=F64, device=self.device)
                 self._hostflags[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, device=self.device)
+                self._hostflags_pinned[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, pin_memory=True)
             off = 0
             for side in range(4):
                 used = gx if side < 2 else gy
@@ -257,9 +259,24 @@ class FusedStencil2D(_PlanBase):
         return [z[gy:gy + ny, 0:2], z[gy:gy + ny, gx + nx:gx + nx + 2], z[0:2, gx:gx + nx],
                 z[gy + ny:gy + ny + 2, gx:gx + nx]][side]
 
+    def publish_host_sides_by_copy(self, rank: int) -> None:
+        """Publish the host-fed sides' flags for the NEXT step with a host-to-device copy on the
+        current stream (enqueue it right after the copy of the values).  A copy engine needs no SM,
+        so this cannot be starved by the very kernel that is waiting for it -- a publishing kernel
+        could be, once the fused kernel's CTAs occupy every SM.  The pinned source holds the epoch
+        of the next step; it is rewritten by the host before every step."""
+        if rank in self._hostflags:
+            self._hostflags_pinned[rank].fill_(self.steps + 1)
+            self._hostflags[rank].copy_(self._hostflags_pinned[rank], non_blocking=True)
+
+    def refresh_host_epoch(self) -> None:
+        """Before replaying a captured step: put the next epoch into the pinned flag sources."""
+        for rank in self._hostflags_pinned:
+            self._hostflags_pinned[rank].fill_(self.steps + 1)
+
     def publish_host_sides(self, rank: int) -> None:
-        """After the host-to-device copy into hostbox[rank] (same stream): mark the host-fed sides of
-        the step that is running / about to run as arrived."""
+        """Kernel flavour, for use on the SAME stream BEFORE the fused kernel (plain step() of a
+        host-fed plan): mark the host-fed sides of the step about to run as arrived."""
         k = self._slot(rank)
         st = torch.cuda.current_stream().cuda_stream
         for (r, side), (_off, _cnt, flags) in self.host_sides.items():

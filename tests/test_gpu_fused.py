@@ -168,3 +168,25 @@ def test_host_fed_sides_behave_like_a_neighbour(dev, px, py):
     r0 = fed.ranks[0]
     side0 = [s for (rr, s) in fed.plan.host_sides if rr == r0][0]
     assert torch.allclose(fed.plan.ghost_view(r0, side0), ref.plan.ghost_view(r0, side0) + 1.0)
+
+
+@pytest.mark.parametrize("oneshot", ["0", "1"])
+def test_host_fed_on_a_full_gpu(dev, monkeypatch, oneshot):
+    """The host-fed flags must arrive although the fused kernel's CTAs occupy every SM slot
+    (persistent mode never frees one before the end): they are published by a copy engine, not by
+    a kernel that would need a slot.  A starved publisher would show up as HaloTimeout."""
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.parallel import runtime
+    monkeypatch.setenv("GMT_FUSED_ONESHOT", oneshot)
+    rt = runtime.init()
+    n = 8192
+    fed = Stencil2DWorkload(rt, n, n, mode="grid", impl="fused", space=VirtualSpace(1, dev), grid=(1, 1),
+                            spin_limit=1 << 24, host_fed=True, with_err=True)
+    fed.setup()
+    fed.e2e_bytes()   # builds the pinned mirror of the boundary values from the (still analytic) ghosts
+    for (rr, side) in fed.plan.host_sides:
+        fed.plan.ghost_view(rr, side).fill_(1e30)
+    errs = [fed.step_e2e() for _ in range(4)]
+    torch.cuda.synchronize()
+    fed.check()
+    assert max(errs) < 1e-4 and errs[0] == pytest.approx(errs[-1], rel=0.1, abs=1e-9)  # atomics: order varies
