@@ -6,7 +6,8 @@ TORCHRUN = $(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node $(NP) --ma
 
 .PHONY: all build force test test-gpu bench sweep sass clean \
         daxpy daxpy_nvtx mpi_daxpy mpi_daxpy_nvtx_managed mpi_daxpy_nvtx_unmanaged mpi_daxpy_gt \
-        mpi_stencil_gt mpi_stencil2d_gt mpi_stencil2d_sycl mpi_stencil2d_sycl_oo mpienv mpigatherinplace
+        mpi_stencil_gt mpi_stencil2d_gt mpi_stencil2d_sycl mpi_stencil2d_sycl_oo mpienv mpigatherinplace \
+        gmt_stencil2d gmt_daxpy
 
 all: build
 
@@ -41,5 +42,9 @@ mpi_daxpy_nvtx_managed:
 mpi_daxpy_nvtx_unmanaged:
 	$(TORCHRUN) -m gpu_mpi_tests_b200.cli.mpi_daxpy_nvtx $(ARGS)
 
+# native programs (C++ on the C ABI, no Python): one process drives every GPU of the node
+gmt_stencil2d gmt_daxpy: build
+	gpu_mpi_tests_b200/_native/bin/$@ $(ARGS)
+
 clean:
-	rm -rf gpu_mpi_tests_b200/_native/obj gpu_mpi_tests_b200/_native/libgmt_b200.so out-*.txt profile
+	rm -rf gpu_mpi_tests_b200/_native/obj gpu_mpi_tests_b200/_native/bin gpu_mpi_tests_b200/_native/libgmt_b200.so out-*.txt profile

@@ -80,7 +80,33 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
         if verbose:
             sys.stderr.write(f"[build] linked {LIB}\n")
+    build_programs(nvcc, verbose)
     return LIB
+
+
+NATIVE_SRC = ROOT / "native"
+BIN_DIR = OUT_DIR / "bin"
+
+
+def build_programs(nvcc: str | None = None, verbose: bool = False) -> list[Path]:
+    """Native programs (native/*.cpp): plain C++ against the C ABI, linked to the in-tree library
+    through an $ORIGIN-relative rpath so the binaries work wherever the tree is copied."""
+    nvcc = nvcc or find_nvcc()
+    BIN_DIR.mkdir(parents=True, exist_ok=True)
+    built = []
+    for src in sorted(NATIVE_SRC.glob("*.cpp")):
+        exe = BIN_DIR / src.stem
+        newest = max(src.stat().st_mtime, LIB.stat().st_mtime, (ROOT / "include" / "gmt_b200.h").stat().st_mtime)
+        if not exe.exists() or exe.stat().st_mtime < newest:
+            cmd = [nvcc, "-O2", "-std=c++17", "-I", str(ROOT / "include"), str(src), "-o", str(exe),
+                   "-L", str(OUT_DIR), "-lgmt_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/..", "-lcudart"]
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if res.returncode != 0:
+                raise RuntimeError(f"building {src.name} failed:\n{res.stdout}\n{res.stderr}")
+            if verbose:
+                sys.stderr.write(f"[build] {exe}\n")
+        built.append(exe)
+    return built
 
 
 if __name__ == "__main__":

@@ -140,6 +140,21 @@ _SIGS = {
     "gmt_daxpy_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_dbl, c_ptr]),
     "gmt_axis_sum_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, c_i64, C.c_int, c_i64, c_ptr]),
     "gmt_barrier": (None, [c_ptr, C.c_int, c_ptr]),
+    # native exchange engine (engine.cu)
+    "gmt_engine_default_device": (None, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
+    "gmt_engine2d_create": (None, [C.c_int, C.c_int, C.POINTER(C.c_int), c_i64, c_i64, C.c_int, C.c_int, C.c_int,
+                                   c_i64, C.POINTER(c_ptr)]),
+    "gmt_engine2d_destroy": (None, [c_ptr]),
+    "gmt_engine2d_world": (C.c_int, [c_ptr]),
+    "gmt_engine2d_device_groups": (C.c_int, [c_ptr]),
+    "gmt_engine2d_rank_device": (None, [c_ptr, C.c_int, C.POINTER(C.c_int)]),
+    "gmt_engine2d_array": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(c_ptr), C.POINTER(c_i64), C.POINTER(c_i64)]),
+    "gmt_engine2d_init_analytic": (None, [c_ptr, C.c_double]),
+    "gmt_engine2d_step": (None, [c_ptr]),
+    "gmt_engine2d_synchronize": (None, [c_ptr]),
+    "gmt_engine2d_status": (None, [c_ptr, C.POINTER(C.c_int)]),
+    "gmt_engine2d_time_steps": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "gmt_engine2d_err_norm": (None, [c_ptr, C.c_int, C.POINTER(C.c_double)]),
 }
 
 

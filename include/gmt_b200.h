@@ -325,6 +325,39 @@ int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int6
 /* signal barrier across ranks (MPI_Barrier, mpi_daxpy_nvtx.cc:277) */
 int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream);
 
+/* ============================================================ native exchange engine
+ * (engine.cu) A whole px x py process grid driven from ONE C/C++ process that owns all GPUs
+ * of the node -- the C++ counterpart of the reference's per-program host orchestration
+ * (neighbours, ghosted arrays, exchange + stencil per iteration, timing:
+ * mpi_stencil2d_gt.cc:385-572) with no Python and no MPI.  Rank r sits at (r % px, r / px),
+ * on devices[r] or, with devices == NULL, on the device the reference's block rule picks
+ * (set_rank_device, mpi_daxpy.cc:36-62: when there are more ranks than GPUs, consecutive
+ * ranks share one).  Neighbouring ranks on different GPUs are wired through CUDA peer
+ * access; ranks sharing a GPU go into one cooperative launch.  Everything is allocated in
+ * create(); step() only launches (one fused halo+stencil kernel per GPU, asynchronous).
+ * Per-rank interior is nx x ny (weak scaling), domain [0,8) per decomposed direction,
+ * z = x^3 + y^2, out = d/dx (gx == 2) + d/dy (gy == 2).  Not thread-safe per engine.    */
+typedef struct gmt_engine2d gmt_engine2d;
+int gmt_engine_default_device(int n_ranks, int rank, int n_devices, int* device);
+int gmt_engine2d_create(int px, int py, const int* devices, int64_t nx, int64_t ny, int gx, int gy,
+                        int with_err, int64_t spin_limit, gmt_engine2d** out);
+int gmt_engine2d_destroy(gmt_engine2d* e);
+int gmt_engine2d_world(const gmt_engine2d* e);
+int gmt_engine2d_device_groups(const gmt_engine2d* e);
+int gmt_engine2d_rank_device(const gmt_engine2d* e, int rank, int* device);
+/* which: 0 = ghosted input z, 1 = result out.  Column-major: `cols` columns of leading dimension ld. */
+int gmt_engine2d_array(const gmt_engine2d* e, int rank, int which, double** ptr, int64_t* cols, int64_t* ld);
+/* analytic field; ghosts analytic on physical sides, `poison` on sides a neighbour must fill */
+int gmt_engine2d_init_analytic(gmt_engine2d* e, double poison);
+int gmt_engine2d_step(gmt_engine2d* e);          /* asynchronous */
+int gmt_engine2d_synchronize(gmt_engine2d* e);
+/* GMT_ETIMEOUT (and the rank) when some rank's bounded flag wait expired */
+int gmt_engine2d_status(gmt_engine2d* e, int* first_bad_rank);
+/* warm-up, then `steps` steps bracketed by CUDA events on every GPU's stream; max over GPUs */
+int gmt_engine2d_time_steps(gmt_engine2d* e, int steps, int warmup, double* ms_per_step);
+/* sqrt of the in-kernel sum((out - analytic)^2) of the last step (needs with_err) */
+int gmt_engine2d_err_norm(gmt_engine2d* e, int rank, double* err_norm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -259,3 +259,18 @@ def test_dist_arrays_world_of_one_cpu(monkeypatch):
         if 1 in dims:
             assert b.ghost(3).shape == (2, 64)
     runtime.finalize()
+
+
+def test_native_engine_device_rule():
+    """gmt_engine_default_device is the reference's set_rank_device rule (mpi_daxpy.cc:36-62);
+    it makes no CUDA call, so it can be checked here through the C ABI."""
+    from gpu_mpi_tests_b200.ops._lib import GmtError, have_native
+    if not have_native():
+        pytest.skip("library not built")
+    from gpu_mpi_tests_b200.parallel.engine import NativeEngine2D
+    from gpu_mpi_tests_b200.parallel.runtime import map_rank_to_device
+    for n_ranks, n_dev in [(8, 8), (4, 8), (16, 8), (42, 6), (1, 1)]:
+        for r in range(n_ranks):
+            assert NativeEngine2D.default_device(n_ranks, r, n_dev) == map_rank_to_device(n_ranks, r, n_dev)[0]
+    with pytest.raises(GmtError, match="not a multiple"):
+        NativeEngine2D.default_device(9, 0, 8)

@@ -1,0 +1,119 @@
+"""Native exchange engine (csrc/engine.cu) and the native program built on it."""
+import re
+import subprocess
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = Path(__file__).resolve().parents[1]
+EXE = ROOT / "gpu_mpi_tests_b200" / "_native" / "bin" / "gmt_stencil2d"
+
+
+def close(a, b, rtol=1e-10):
+    return bool(((a - b).abs() <= rtol * (1.0 + b.abs())).all())
+
+
+@pytest.mark.parametrize("px,py,gx,gy", [(2, 2, 2, 2), (4, 1, 2, 0), (1, 3, 0, 2), (1, 1, 2, 2)])
+def test_engine_matches_python_plan(px, py, gx, gy):
+    """Same grid through the C++ engine (all ranks on GPU 0, one cooperative launch) and through
+    the Python plan on virtual ranks: same result arrays, same landed ghosts, same error norm."""
+    from gpu_mpi_tests_b200.parallel.engine import NativeEngine2D
+    from gpu_mpi_tests_b200.parallel.halo import FusedStencil2D
+    from gpu_mpi_tests_b200.parallel.symm import VirtualSpace
+    dev = torch.device("cuda", 0)
+    nx, ny = 1536, 320
+    world = px * py
+    eng = NativeEngine2D(px, py, nx, ny, gx, gy, with_err=True, devices=[0] * world, spin_limit=1 << 26)
+    plan = FusedStencil2D(VirtualSpace(world, dev), px, py, nx, ny, gx, gy, with_err=True, spin_limit=1 << 26)
+    eng.init_analytic(poison=1e30)
+    plan.init_analytic(poison=1e30)
+    for _ in range(3):   # both parities and a repeat
+        eng.step()
+        plan.step()
+    eng.synchronize()
+    torch.cuda.synchronize()
+    eng.check()
+    plan.check_status()
+    assert eng.world == world and eng.n_device_groups == 1
+    for r in range(world):
+        assert close(eng.array(r, "out"), plan.out[r]), f"rank {r}"
+        assert torch.equal(eng.array(r, "z"), plan.z[r]), f"rank {r}: ghosts"
+        assert eng.err_norm(r) == pytest.approx(plan.err_norm(r), rel=0.1, abs=1e-9)
+        assert eng.err_norm(r) < 1e-3
+    eng.close()
+
+
+def test_engine_timing_and_argument_checks():
+    from gpu_mpi_tests_b200.ops._lib import GmtError
+    from gpu_mpi_tests_b200.parallel.engine import NativeEngine2D
+    eng = NativeEngine2D(2, 1, 2048, 1024, 2, 2, devices=[0, 0])
+    eng.init_analytic()
+    ms = eng.time_steps(5, 2)
+    assert 0.0 < ms < 100.0
+    assert max(eng.err_norm(r) for r in range(2)) < 1e-3
+    eng.close()
+    with pytest.raises(GmtError):
+        NativeEngine2D(2, 1, 2048, 1024, 0, 2, devices=[0, 0])   # px > 1 without x ghosts
+    with pytest.raises(GmtError):
+        NativeEngine2D(1, 1, 2050, 1024, 2, 2)                  # nx % 4
+    with pytest.raises(GmtError):
+        NativeEngine2D(1, 1, 2048, 1024, 2, 2, devices=[99])
+
+
+def test_engine_across_gpus():
+    """One rank per GPU, peers wired through CUDA peer access inside one process."""
+    from gpu_mpi_tests_b200.parallel.engine import NativeEngine2D
+    n_dev = torch.cuda.device_count()
+    if n_dev < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 4 if n_dev >= 4 else 2
+    px, py = (2, 2) if world == 4 else (2, 1)
+    eng = NativeEngine2D(px, py, 4096, 2048, 2, 2)
+    assert eng.n_device_groups == world and [eng.rank_device(r) for r in range(world)] == list(range(world))
+    eng.init_analytic(poison=1e30)
+    ms = eng.time_steps(10, 3)
+    assert ms > 0
+    for r in range(world):
+        assert eng.err_norm(r) < 1e-3, f"rank {r}"     # a stale ghost would give ~1e30
+    before = torch.cuda.current_device()
+    eng.step()
+    eng.synchronize()
+    assert torch.cuda.current_device() == before
+    eng.close()
+
+
+def test_native_program_runs():
+    assert EXE.exists(), f"{EXE} missing: run python -m gpu_mpi_tests_b200._native.build"
+    res = subprocess.run([str(EXE), "256", "3", "--ranks", "4", "--other", "4096", "--tile", "1024"],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = res.stdout
+    assert "n procs        = 4" in out and "n_global_deriv = 1024" in out
+    tests = re.findall(r"^TEST (dim:0|dim:1|grid ), device , fused; ([0-9.]+), err=([0-9.eE+-]+)$", out, re.M)
+    assert [t[0] for t in tests] == ["dim:0", "dim:1", "grid "], out
+    for _label, secs, err in tests:
+        assert float(secs) > 0 and float(err) < 1e-3
+
+
+def test_native_program_rejects_uneven_oversubscription():
+    n_dev = torch.cuda.device_count()
+    if n_dev < 2:
+        pytest.skip("with one GPU every rank count divides")
+    res = subprocess.run([str(EXE), "256", "1", "--ranks", str(n_dev + 1)], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 1
+    assert "not a multiple of number of GPUs" in res.stderr
+
+
+def test_native_daxpy_program():
+    """daxpy.cu's contract: n element lines then SUM = 524800.000000 (daxpy.cu:84-87)."""
+    exe = EXE.parent / "gmt_daxpy"
+    res = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout + res.stderr
+    lines = res.stdout.strip().splitlines()
+    assert len(lines) == 1025 and lines[0] == "1.000000" and lines[1023] == "1024.000000"
+    assert lines[-1] == "SUM = 524800.000000"
+    res = subprocess.run([str(exe), "1048576", "--quiet"], capture_output=True, text=True, timeout=120)
+    assert res.stdout.strip() == "SUM = %f" % (1048576 * 1048577 / 2)
