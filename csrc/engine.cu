@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "engine_util.h"
 
 namespace {
 
@@ -64,19 +65,8 @@ int neighbour(const gmt_engine2d* e, int rank, int side)
   return (cx >= 0 && cx < e->px && cy >= 0 && cy < e->py) ? cx + cy * e->px : -1;
 }
 
-// the engine hops between devices; callers (e.g. a torch process) get their current device back
-struct DeviceRestore {
-  int dev = -1;
-  DeviceRestore() { if (cudaGetDevice(&dev) != cudaSuccess) dev = -1; }
-  ~DeviceRestore() { if (dev >= 0) cudaSetDevice(dev); }
-};
-
-size_t take(size_t& cursor, size_t bytes)
-{
-  const size_t at = cursor;
-  cursor += (bytes + 255) & ~size_t(255);
-  return at;
-}
+using gmt::DeviceRestore;
+using gmt::take;
 
 int free_all(gmt_engine2d* e)
 {
@@ -161,16 +151,14 @@ int gmt_engine2d_create(int px, int py, const int* devices, int64_t nx, int64_t 
     e->ranks[r].device = d;
     e->ranks[r].cx = r % px, e->ranks[r].cy = r / px;
   }
-  // device groups in first-seen order
-  for (int r = 0; r < world; ++r) {
-    auto it = std::find_if(e->groups.begin(), e->groups.end(),
-                           [&](const DeviceGroup& g) { return g.device == e->ranks[r].device; });
-    if (it == e->groups.end()) {
+  {
+    std::vector<int> dev_of(world);
+    for (int r = 0; r < world; ++r) dev_of[r] = e->ranks[r].device;
+    for (const auto& dr : gmt::group_by_device(dev_of)) {
       e->groups.emplace_back();
-      it = e->groups.end() - 1;
-      it->device = e->ranks[r].device;
+      e->groups.back().device = dr.device;
+      e->groups.back().ranks = dr.ranks;
     }
-    it->ranks.push_back(r);
   }
   // peer access between every pair of devices that host neighbouring ranks
   for (int r = 0; r < world; ++r)

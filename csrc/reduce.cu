@@ -175,6 +175,16 @@ __global__ void __launch_bounds__(512)
     x[i] = (start + (double)i * step) * mul;
 }
 
+// x[i-1] = (rank * i) / N in INTEGER arithmetic, i = 1..n: the slot pattern of the reference's
+// in-place gather test (mpigatherinplace.f90:34-37), done in 64 bits (the Fortran default
+// integers overflow at >= 16 ranks).
+__global__ void __launch_bounds__(512) slot_pattern_kernel(int64_t n, int64_t rank, int64_t N, double* x)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    x[i] = (double)((rank * (i + 1)) / N);
+}
+
 // dst(i,j) = src(i,j).  The interesting shapes are the halo strips: rows = 2 with half a
 // million columns (dim 0: one 16-byte element pair every ld doubles) and rows = 524288 with
 // 2 columns (dim 1: two long contiguous runs).  Threads are flattened over (i,j) with i
@@ -296,6 +306,15 @@ int gmt_iota_f64(int64_t n, double start, double step, double mul, double* x, gm
   if (n == 0) return 0;
   gmt::iota_kernel<<<gmt::grid_for(n, 512, 4), 512, 0, gmt::as_stream(stream)>>>(n, start, step, mul,
                                                                                x);
+  GMT_LAUNCH_CHECK();
+  return 0;
+}
+
+int gmt_slot_pattern_f64(int64_t n, int64_t rank, int64_t N, double* x, gmt_stream_t stream)
+{
+  GMT_REQUIRE(n >= 0 && N > 0 && rank >= 0 && (n == 0 || x), GMT_EINVAL, "gmt_slot_pattern_f64: bad argument");
+  if (n == 0) return 0;
+  gmt::slot_pattern_kernel<<<gmt::grid_for(n, 512, 4), 512, 0, gmt::as_stream(stream)>>>(n, rank, N, x);
   GMT_LAUNCH_CHECK();
   return 0;
 }

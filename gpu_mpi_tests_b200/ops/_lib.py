@@ -121,6 +121,7 @@ _SIGS = {
     "gmt_fill_f64": (None, [c_i64, c_dbl, c_ptr, c_ptr]),
     "gmt_fill_u64": (None, [c_i64, C.c_uint64, c_ptr, c_ptr]),
     "gmt_iota_f64": (None, [c_i64, c_dbl, c_dbl, c_dbl, c_ptr, c_ptr]),
+    "gmt_slot_pattern_f64": (None, [c_i64, c_i64, c_i64, c_ptr, c_ptr]),
     "gmt_stencil1d_f64": (None, [c_i64, c_ptr, c_ptr, c_dbl, C.c_int, c_ptr]),
     "gmt_stencil2d_f64": (None, [C.c_int, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, C.c_int, c_ptr]),
     "gmt_stencil2d_d1_cluster_f64": (None, [c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_dbl, c_ptr]),
@@ -155,6 +156,25 @@ _SIGS = {
     "gmt_engine2d_status": (None, [c_ptr, C.POINTER(C.c_int)]),
     "gmt_engine2d_time_steps": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "gmt_engine2d_err_norm": (None, [c_ptr, C.c_int, C.POINTER(C.c_double)]),
+    # native collective engine (engine_coll.cu)
+    "gmt_coll_engine_create": (None, [C.c_int, C.POINTER(C.c_int), c_i64, c_i64, c_i64, C.POINTER(c_ptr)]),
+    "gmt_coll_engine_destroy": (None, [c_ptr]),
+    "gmt_coll_engine_world": (C.c_int, [c_ptr]),
+    "gmt_coll_engine_device_groups": (C.c_int, [c_ptr]),
+    "gmt_coll_engine_rank_device": (None, [c_ptr, C.c_int, C.POINTER(C.c_int)]),
+    "gmt_coll_engine_buffer": (None, [c_ptr, C.c_int, C.POINTER(c_ptr), C.POINTER(c_i64)]),
+    "gmt_coll_engine_stream": (None, [c_ptr, C.c_int, C.POINTER(c_ptr)]),
+    "gmt_coll_engine_bind": (None, [c_ptr, C.c_int, c_ptr, c_ptr, c_ptr]),
+    "gmt_coll_engine_allgather": (None, [c_ptr, c_i64, C.c_int]),
+    "gmt_coll_engine_gather": (None, [c_ptr, c_i64, C.c_int]),
+    "gmt_coll_engine_allreduce": (None, [c_ptr, c_i64, C.c_int]),
+    "gmt_coll_engine_daxpy_allreduce": (None, [c_ptr, c_i64, c_dbl]),
+    "gmt_coll_engine_axis_sum_allreduce": (None, [c_ptr, c_i64, c_i64, c_i64, C.c_int, c_i64]),
+    "gmt_coll_engine_barrier": (None, [c_ptr]),
+    "gmt_coll_engine_synchronize": (None, [c_ptr]),
+    "gmt_coll_engine_status": (None, [c_ptr, C.POINTER(C.c_int)]),
+    "gmt_coll_engine_mark": (None, [c_ptr, C.c_int]),
+    "gmt_coll_engine_elapsed_ms": (None, [c_ptr, C.POINTER(C.c_double)]),
 }
 
 

@@ -88,3 +88,86 @@ class NativeEngine2D:
         v = C.c_double()
         lib.gmt_engine2d_err_norm(self._h, rank, C.byref(v))
         return v.value
+
+
+class NativeCollectives:
+    """Handle on the native collective engine (csrc/engine_coll.cu): `world` ranks placed on the
+    GPUs of this process, symmetric buffers wired through CUDA peer access, one launch per GPU
+    per collective on the engine's own per-GPU streams."""
+
+    def __init__(self, world: int, buf_doubles: int = 0, stage_cap: int = 4096, devices: list[int] | None = None,
+                 spin_limit: int = 0):
+        require_native()
+        self._h = C.c_void_p()
+        dev_arr = (C.c_int * world)(*devices) if devices is not None else None
+        lib.gmt_coll_engine_create(world, dev_arr, buf_doubles, stage_cap, spin_limit, C.byref(self._h))
+        self.world = int(lib.gmt_coll_engine_world(self._h))
+        self.n_device_groups = int(lib.gmt_coll_engine_device_groups(self._h))
+        self._keep = {}
+
+    def close(self) -> None:
+        if self._h:
+            lib.gmt_coll_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):  # noqa: D105
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def rank_device(self, rank: int) -> int:
+        d = C.c_int()
+        lib.gmt_coll_engine_rank_device(self._h, rank, C.byref(d))
+        return d.value
+
+    def buffer(self, rank: int) -> torch.Tensor:
+        p, n = C.c_void_p(), C.c_int64()
+        lib.gmt_coll_engine_buffer(self._h, rank, C.byref(p), C.byref(n))
+        dev = torch.device("cuda", self.rank_device(rank))
+        with torch.cuda.device(dev):
+            return torch.as_tensor(_DevPtr(p.value, (n.value,), self), device=dev)
+
+    def stream(self, rank: int) -> "torch.cuda.ExternalStream":
+        s = C.c_void_p()
+        lib.gmt_coll_engine_stream(self._h, rank, C.byref(s))
+        return torch.cuda.ExternalStream(s.value, device=torch.device("cuda", self.rank_device(rank)))
+
+    def bind(self, rank: int, inp=None, out=None, y=None) -> None:
+        self._keep[rank] = (inp, out, y)   # keep the operands alive while the engine points at them
+        ptr = lambda t: None if t is None else C.c_void_p(t.data_ptr())  # noqa: E731
+        lib.gmt_coll_engine_bind(self._h, rank, ptr(inp), ptr(out), ptr(y))
+
+    def allgather(self, n: int, from_in: bool = False) -> None:
+        lib.gmt_coll_engine_allgather(self._h, n, int(from_in))
+
+    def gather(self, n: int, root: int = 0) -> None:
+        lib.gmt_coll_engine_gather(self._h, n, root)
+
+    def allreduce(self, n: int, algo: int = 0) -> None:
+        lib.gmt_coll_engine_allreduce(self._h, n, algo)
+
+    def daxpy_allreduce(self, n: int, a: float) -> None:
+        lib.gmt_coll_engine_daxpy_allreduce(self._h, n, float(a))
+
+    def axis_sum_allreduce(self, nx: int, ny: int, ld: int, axis: int, n_out: int) -> None:
+        lib.gmt_coll_engine_axis_sum_allreduce(self._h, nx, ny, ld, axis, n_out)
+
+    def barrier(self) -> None:
+        lib.gmt_coll_engine_barrier(self._h)
+
+    def synchronize(self) -> None:
+        lib.gmt_coll_engine_synchronize(self._h)
+
+    def check(self) -> None:
+        lib.gmt_coll_engine_status(self._h, None)
+
+    def timed(self, fn, iters: int = 1) -> float:
+        """Device milliseconds per call of fn(), max over the GPUs."""
+        lib.gmt_coll_engine_mark(self._h, 0)
+        for _ in range(iters):
+            fn()
+        lib.gmt_coll_engine_mark(self._h, 1)
+        ms = C.c_double()
+        lib.gmt_coll_engine_elapsed_ms(self._h, C.byref(ms))
+        return ms.value / iters

@@ -138,6 +138,9 @@ int gmt_fill_f64(int64_t n, double value, double* x, gmt_stream_t stream);
 int gmt_fill_u64(int64_t n, uint64_t value, uint64_t* x, gmt_stream_t stream);
 /* x[i] <- (start + i*step)*mul   -- daxpy initialisers (mpi_daxpy_nvtx.cc:209-212) */
 int gmt_iota_f64(int64_t n, double start, double step, double mul, double* x, gmt_stream_t stream);
+/* x[i-1] <- (rank*i)/N in 64-bit integer arithmetic, i = 1..n: the slot values of the in-place
+ * gather test (mpigatherinplace.f90:34-37) */
+int gmt_slot_pattern_f64(int64_t n, int64_t rank, int64_t N, double* x, gmt_stream_t stream);
 
 /* 5-point 4th-order first derivative, out[i] = scale * sum_k c_k in[i+k], k=0..4
  * (stencil1d_5, mpi_stencil_gt.cc:54-59).  in has n+4 elements.
@@ -357,6 +360,37 @@ int gmt_engine2d_status(gmt_engine2d* e, int* first_bad_rank);
 int gmt_engine2d_time_steps(gmt_engine2d* e, int steps, int warmup, double* ms_per_step);
 /* sqrt of the in-kernel sum((out - analytic)^2) of the last step (needs with_err) */
 int gmt_engine2d_err_norm(gmt_engine2d* e, int rank, double* err_norm);
+
+/* Collective engine (engine_coll.cu): the same single-process arrangement for the collectives --
+ * the host side of the reference's daxpy benchmark and gather test (mpi_daxpy_nvtx.cc:85-343,
+ * mpigatherinplace.f90:1-58).  Every rank owns a symmetric user buffer of buf_doubles doubles
+ * (gathered arrays live there) and a staging area of 4*stage_cap doubles; each call below is one
+ * asynchronous launch per GPU on the engine's per-GPU stream (gmt_coll_engine_stream: order your
+ * own work on a rank's operands on that stream).  No NVLS multicast variants here.            */
+typedef struct gmt_coll_engine gmt_coll_engine;
+int gmt_coll_engine_create(int world, const int* devices, int64_t buf_doubles, int64_t stage_cap,
+                           int64_t spin_limit, gmt_coll_engine** out);
+int gmt_coll_engine_destroy(gmt_coll_engine* e);
+int gmt_coll_engine_world(const gmt_coll_engine* e);
+int gmt_coll_engine_device_groups(const gmt_coll_engine* e);
+int gmt_coll_engine_rank_device(const gmt_coll_engine* e, int rank, int* device);
+int gmt_coll_engine_buffer(const gmt_coll_engine* e, int rank, double** ptr, int64_t* doubles);
+int gmt_coll_engine_stream(const gmt_coll_engine* e, int rank, gmt_stream_t* stream);
+/* local operands of a rank for the next calls (see gmt_coll_rank.in/out/y); stream-ordered */
+int gmt_coll_engine_bind(gmt_coll_engine* e, int rank, const double* in, double* out, double* y);
+int gmt_coll_engine_allgather(gmt_coll_engine* e, int64_t n, int from_in);
+int gmt_coll_engine_gather(gmt_coll_engine* e, int64_t n, int root);
+int gmt_coll_engine_allreduce(gmt_coll_engine* e, int64_t n, int algo);
+int gmt_coll_engine_daxpy_allreduce(gmt_coll_engine* e, int64_t n, double a);
+int gmt_coll_engine_axis_sum_allreduce(gmt_coll_engine* e, int64_t nx, int64_t ny, int64_t ld, int axis,
+                                       int64_t n_out);
+int gmt_coll_engine_barrier(gmt_coll_engine* e);
+int gmt_coll_engine_synchronize(gmt_coll_engine* e);
+int gmt_coll_engine_status(gmt_coll_engine* e, int* first_bad_rank);
+/* device timing: mark(0) / mark(1) record an event on every GPU's stream; elapsed_ms waits for
+ * the second marks and returns the largest per-GPU interval */
+int gmt_coll_engine_mark(gmt_coll_engine* e, int which);
+int gmt_coll_engine_elapsed_ms(gmt_coll_engine* e, double* ms);
 
 #ifdef __cplusplus
 }

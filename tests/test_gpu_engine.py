@@ -117,3 +117,108 @@ def test_native_daxpy_program():
     assert lines[-1] == "SUM = 524800.000000"
     res = subprocess.run([str(exe), "1048576", "--quiet"], capture_output=True, text=True, timeout=120)
     assert res.stdout.strip() == "SUM = %f" % (1048576 * 1048577 / 2)
+
+
+def _coll_devices(world):
+    """All ranks on GPU 0 on a 1-GPU box; spread by the block rule when there are more GPUs."""
+    n_dev = torch.cuda.device_count()
+    if n_dev >= 2 and world % 2 == 0:
+        return None if world % n_dev == 0 or world <= n_dev else [r * 2 // world for r in range(world)]
+    return [0] * world
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_native_collectives(world):
+    from gpu_mpi_tests_b200.parallel.engine import NativeCollectives
+    n = 3000
+    eng = NativeCollectives(world, buf_doubles=n * world, stage_cap=2048, devices=_coll_devices(world),
+                            spin_limit=1 << 26)
+    devs = [torch.device("cuda", eng.rank_device(r)) for r in range(world)]
+    gen = torch.Generator().manual_seed(5)
+    slices = [torch.randn(n, dtype=torch.float64, generator=gen) for _ in range(world)]
+    want = torch.cat(slices)
+    # in-place allgather
+    for r in range(world):
+        with torch.cuda.stream(eng.stream(r)):
+            b = eng.buffer(r)
+            b.fill_(-7.0)
+            b[r * n:(r + 1) * n].copy_(slices[r].to(devs[r]))
+    eng.synchronize()
+    eng.allgather(n)
+    eng.allgather(n)   # twice: epochs / rounds must not interfere
+    eng.synchronize()
+    eng.check()
+    for r in range(world):
+        assert torch.equal(eng.buffer(r).cpu(), want), f"rank {r}"
+    # out-of-place source + gather to root
+    srcs = [(slices[r] * 2).to(devs[r]) for r in range(world)]
+    for r in range(world):
+        eng.bind(r, inp=srcs[r])
+    eng.allgather(n, from_in=True)
+    eng.synchronize()
+    for r in range(world):
+        assert torch.equal(eng.buffer(r).cpu(), want * 2), f"rank {r}"
+    # all-reduce (both algorithms), identical bits on every rank
+    vecs = [torch.randn(1024, dtype=torch.float64, generator=gen) for _ in range(world)]
+    total = torch.stack(vecs).sum(0)
+    for algo in (0, 1):
+        ins = [v.to(d) for v, d in zip(vecs, devs)]
+        outs = [torch.zeros(1024, dtype=torch.float64, device=d) for d in devs]
+        for r in range(world):
+            eng.bind(r, inp=ins[r], out=outs[r])
+        eng.allreduce(1024, algo)
+        eng.synchronize()
+        eng.check()
+        for r in range(world):
+            assert torch.allclose(outs[r].cpu(), total, rtol=1e-13, atol=1e-13)
+            assert torch.equal(outs[r].cpu(), outs[0].cpu())
+    # fused daxpy + global sum
+    m = 1 << 18
+    xs = [torch.randn(m, dtype=torch.float64, generator=gen).to(d) for d in devs]
+    ys = [torch.randn(m, dtype=torch.float64, generator=gen).to(d) for d in devs]
+    ref = sum(float((2.0 * x.cpu() + y.cpu()).sum()) for x, y in zip(xs, ys))
+    sums = [torch.zeros(8, dtype=torch.float64, device=d) for d in devs]
+    torch.cuda.synchronize()
+    for r in range(world):
+        eng.bind(r, inp=xs[r], out=sums[r], y=ys[r])
+    eng.daxpy_allreduce(m, 2.0)
+    eng.barrier()
+    eng.synchronize()
+    eng.check()
+    for r in range(world):
+        assert float(sums[r][0]) == pytest.approx(ref, rel=1e-11, abs=1e-8)
+    ms = eng.timed(lambda: eng.barrier(), iters=10)
+    assert 0 < ms < 50
+    from gpu_mpi_tests_b200.ops._lib import GmtError
+    with pytest.raises(GmtError):
+        eng.allgather(n + 1)
+    with pytest.raises(GmtError):
+        eng.allreduce(4096, 0)
+    eng.close()
+
+
+@pytest.mark.parametrize("ranks", [1, 4])
+def test_native_daxpy_gather_program(ranks):
+    n_dev = torch.cuda.device_count()
+    if ranks > n_dev and ranks % n_dev:
+        pytest.skip("rank count does not divide")
+    exe = EXE.parent / "gmt_daxpy_gather"
+    n = 1 << 20
+    res = subprocess.run([str(exe), "--n", str(n), "--ranks", str(ranks), "--barrier"], capture_output=True, text=True,
+                         timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = res.stdout
+    assert f"1 nodes, {ranks} ranks, {n} elements each, total {n * ranks}" in out
+    for r in range(ranks):
+        assert f"{r}/{ranks} SUM = {(n + 1) / 2:f}" in out
+        assert f"{r}/{ranks} ALLSUM = {ranks * (n + 1) / 2:f}" in out
+        assert re.search(rf"^{r}/{ranks} TIME gather : [0-9.]+$", out, re.M)
+
+
+@pytest.mark.parametrize("args", [[], ["--gather", "1"]])
+def test_native_gatherinplace_program(args):
+    exe = EXE.parent / "gmt_gatherinplace"
+    res = subprocess.run([str(exe), str(1 << 20), "--ranks", "4", *args], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr   # the program checks the closed-form sums itself
+    rows = re.findall(r"^ (\d) / 4   ([0-9.]+)   ([0-9.]+)$", res.stdout, re.M)
+    assert len(rows) == 4
