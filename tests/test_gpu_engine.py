@@ -222,3 +222,19 @@ def test_native_gatherinplace_program(args):
     assert res.returncode == 0, res.stdout + res.stderr   # the program checks the closed-form sums itself
     rows = re.findall(r"^ (\d) / 4   ([0-9.]+)   ([0-9.]+)$", res.stdout, re.M)
     assert len(rows) == 4
+
+
+def test_native_stencil1d_program():
+    """Hand-wired descriptors against the C ABI (native/gmt_stencil1d.cpp), on every GPU."""
+    exe = EXE.parent / "gmt_stencil1d"
+    res = subprocess.run([str(exe), "8", "--iters", "5"], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr   # the program itself checks err_norm and status
+    W = torch.cuda.device_count()
+    assert f"n procs  = {W}\nn_global = {8 << 20}\nn_local  = {(8 << 20) // W}" in res.stdout
+    for r in range(W):
+        assert re.search(rf"^{r}/{W} exchange time [0-9.]+$", res.stdout, re.M)
+        assert re.search(rf"^{r}/{W} \[{r}:0x[0-9a-f]{{8}}\] err_norm = [0-9.]+$", res.stdout, re.M)
+    res = subprocess.run([str(exe), "--points", str(1000 * W + 1), "--ranks", str(W)], capture_output=True,
+                         text=True, timeout=60)
+    if W > 1:
+        assert res.returncode == 1 and "must be divisor of domain size" in res.stdout
