@@ -26,7 +26,44 @@ def device_line(rt) -> str:
     return report.sycl_device_line(rt.rank, bdf, uuid)
 
 
-def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_style: str):
+def _rank_by_rank(rt, fn) -> None:
+    """Run fn() on one rank at a time, separated by barriers (the DEBUG build's dump loop,
+    mpi_stencil2d_sycl_oo.cc:636-659)."""
+    for turn in range(rt.world_size):
+        if turn == rt.rank:
+            fn()
+            sys.stderr.flush()
+        rt.barrier()
+
+
+def debug_dump_boundary_rows(rt, z, n_bnd: int = 2) -> None:
+    """DEBUG build: the two boundary rows a rank is about to send on each side, first 20 columns
+    (mpi_stencil2d_sycl_oo.cc:641-654).  z is the column-major array as torch [j, i]."""
+    nrows, ncols = z.shape[1], z.shape[0]
+
+    def dump():
+        for i in list(range(n_bnd, 2 * n_bnd)) + list(range(nrows - 2 * n_bnd, nrows - n_bnd)):
+            vals = " ".join("%f" % v for v in z[:min(20, ncols), i].tolist())
+            sys.stderr.write("%d: [%d, :] %s\n" % (rt.rank, i, vals))
+    _rank_by_rank(rt, dump)
+
+
+def debug_dump_ghosts(rt, z, has_left: bool, has_right: bool, n_bnd: int = 2, limit: int = 20) -> None:
+    """DEBUG build: what arrived in the ghost rows (the reference prints its receive buffers,
+    mpi_stencil2d_sycl_oo.cc:481-505); bounded to `limit` columns."""
+    nrows, ncols = z.shape[1], z.shape[0]
+
+    def dump():
+        for name, has, row0 in (("rbuf_l", has_left, 0), ("rbuf_r", has_right, nrows - n_bnd)):
+            if not has:
+                continue
+            for i in range(min(limit, ncols)):
+                for j in range(n_bnd):
+                    sys.stderr.write("%d: %s[%d, %d] = %f\n" % (rt.rank, name, j, i, float(z[i, row0 + j])))
+    _rank_by_rank(rt, dump)
+
+
+def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_style: str, debug: bool = False):
     space = make_space(rt) if impl == "fused" else None
     r, W = rt.rank, rt.world_size
     if impl == "baseline":
@@ -35,6 +72,8 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
     else:
         wl = Stencil2DWorkload(rt, nx_local, ny, mode="dim0", impl="fused", with_err=False, space=space)
     wl.setup()
+    if debug:
+        debug_dump_boundary_rows(rt, wl.z[r])
     total = 0.0
     if impl == "baseline":
         for i in range(n_warmup + n_iter):
@@ -62,6 +101,10 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
         torch.cuda.synchronize()
         total = max(0.0, (e0.elapsed_time(e1) - e1.elapsed_time(e2)) * 1e-3)
         wl.step()
+    if debug:
+        if rt.is_cuda:
+            torch.cuda.synchronize()
+        debug_dump_ghosts(rt, wl.z[r], r > 0, r < W - 1)
     ms = total / max(n_iter, 1) * 1000
     err = wl.err_norm(r)
     wl.check()

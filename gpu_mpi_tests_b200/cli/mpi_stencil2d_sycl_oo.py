@@ -1,7 +1,8 @@
 """mpi_stencil2d_sycl_oo (mpi_stencil2d_sycl_oo.cc:517-705): the dim-0 case on a SQUARE global
 domain with small array classes.  argv: [n_global_Ki=8] [stage_host] [n_iter=100]; n_global =
 argv*1024 must divide by the rank count; slab along dim 0; warm-up 5.  --debug shrinks to
-n_global/1024 points, 1 iteration, no warm-up (the DEBUG build)."""
+n_global/1024 points, 1 iteration, no warm-up and dumps the boundary rows and the received
+ghost rows rank by rank on stderr (the DEBUG build, mpi_stencil2d_sycl_oo.cc:545-549,636-659)."""
 from __future__ import annotations
 
 import sys
@@ -30,7 +31,7 @@ def _main(argv=None) -> int:
     if impl == "fused" and slab.n_local % 4:
         out("n_local is not a multiple of 4: using the baseline exchange")
         impl = "baseline"
-    run_dim0(rt, out, impl, slab.n_local, n_global, n_iter, n_warmup, stage_host, "oo")
+    run_dim0(rt, out, impl, slab.n_local, n_global, n_iter, n_warmup, stage_host, "oo", debug=args.debug)
     _common.finish(rt)
     return 0
 

@@ -147,7 +147,7 @@ int gmt_slot_pattern_f64(int64_t n, int64_t rank, int64_t N, double* x, gmt_stre
  * variant: 0 = one thread per point (mirrors a generic expression kernel),
  *          1 = 256-bit vectorised streaming kernel,
  *          2 = TMA: cp.async.bulk + mbarrier pipeline (1-D); for the 2-D dim-1 stencil,
- *              tensor-map loads + 2-CTA clusters sharing halo columns over DSMEM
+ *              tensor-map loads + 2-CTA clusters, shared halo columns fetched once by TMA multicast
  *              (2-D dim 0 has no TMA variant and runs variant 1).             */
 int gmt_stencil1d_f64(int64_t n, const double* in, double* out, double scale, int variant,
                       gmt_stream_t stream);
@@ -158,8 +158,8 @@ int gmt_stencil1d_f64(int64_t n, const double* in, double* out, double scale, in
 int gmt_stencil2d_f64(int dim, int64_t nx, int64_t ny, const double* z, int64_t ldz, double* dz,
                       int64_t lddz, double scale, int variant, gmt_stream_t stream);
 /* variant 2 of the dim-1 stencil on its own: 2-D TMA tensor-map loads + thread-block clusters
- * of two CTAs sharing their halo columns over distributed shared memory (no reference
- * counterpart; see csrc/stencil_tma.cu for the shape/alignment requirements)            */
+ * of two CTAs; the 4 halo columns between their tiles are fetched once and delivered to both
+ * CTAs' shared memory by TMA multicast (no reference counterpart; see csrc/stencil_tma.cu for the shape/alignment requirements)            */
 int gmt_stencil2d_d1_cluster_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,
                                  int64_t ldo, double scale, gmt_stream_t stream);
 /* cross stencil on a (nx+4, ny+4) array ghosted in both dims:

@@ -13,7 +13,7 @@ ROOT = Path(__file__).resolve().parents[1]
 _port = [29800 + (os.getpid() % 150)]
 
 
-def run_cli(module, *args, nproc=1, env_extra=None, cpu=True, timeout=600, expect_rc=0):
+def run_cli(module, *args, nproc=1, env_extra=None, cpu=True, timeout=600, expect_rc=0, with_stderr=False):
     env = dict(os.environ)
     if cpu:
         env["GMT_FORCE_CPU"] = "1"
@@ -29,7 +29,8 @@ def run_cli(module, *args, nproc=1, env_extra=None, cpu=True, timeout=600, expec
                f"gpu_mpi_tests_b200.cli.{module}", *map(str, args)]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
     assert res.returncode == expect_rc, f"{module}: rc={res.returncode}\n{res.stdout[-2000:]}\n{res.stderr[-3000:]}"
-    return [ln for ln in res.stdout.splitlines() if ln.strip()]
+    lines = [ln for ln in res.stdout.splitlines() if ln.strip()]
+    return (lines, res.stderr.splitlines()) if with_stderr else lines
 
 
 def match_all(lines, patterns):
@@ -119,6 +120,31 @@ def test_sycl_variants_world2():
                       rf"0/2 exchange time {F8} ms", rf"1/2 \[1:0x[0-9a-f]{{8}}\] err_norm = {F8}"])
     lines = run_cli("mpi_stencil2d_sycl_oo", 1, 0, 2, nproc=2)
     match_all(lines, [r"n_global   = 1024", r"n_local    = 512", rf"0: exchange time {F8} ms", rf"1: \[0x[0-9a-f]{{8}}\] err_norm = {F8}"])
+
+
+def test_sycl_oo_debug_dumps_world2():
+    """--debug = the reference's DEBUG build: tiny domain, 1 iteration, boundary rows and received
+    ghost rows dumped rank by rank on stderr (mpi_stencil2d_sycl_oo.cc:545-549,636-659,481-505)."""
+    lines, err = run_cli("mpi_stencil2d_sycl_oo", 16, 0, 7, "--debug", nproc=2, with_stderr=True)
+    match_all(lines, [r"n_global   = 16", r"n_local    = 8", r"n_iter     = 1", r"n_warmup   = 0"])
+    rows = [ln for ln in err if re.match(r"\d: \[\d+, :\]", ln)]
+    assert len(rows) == 8                                   # 2 + 2 boundary rows per rank
+    assert [ln[0] for ln in rows] == ["0"] * 4 + ["1"] * 4   # rank 0's block first, then rank 1's
+    assert all(len(ln.split()) == 3 + 16 for ln in rows)    # "r: [i, :]" + min(20, 16) values
+    # rank 0 receives from its right neighbour only, rank 1 from its left neighbour only
+    got = [ln for ln in err if "rbuf_" in ln]
+    assert {ln.split("[")[0] for ln in got} == {"0: rbuf_r", "1: rbuf_l"}
+    # what rank 1 received on its left is what rank 0 dumped as its last two interior rows
+    sent = [float(v) for ln in rows[2:4] for v in ln.split()[3:]]              # rows 8, 9 of rank 0, 16 columns each
+    recv = {}
+    for ln in got:
+        m = re.fullmatch(r"1: rbuf_l\[(\d+), (\d+)\] = (-?[0-9.]+)", ln)
+        if m:
+            recv[(int(m.group(1)), int(m.group(2)))] = float(m.group(3))
+    assert len(recv) == 32
+    for j in range(2):
+        for i in range(16):
+            assert recv[(j, i)] == pytest.approx(sent[j * 16 + i], abs=1e-6)
 
 
 def test_rank_device_ratio_error_exit1():
