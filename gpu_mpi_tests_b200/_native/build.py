@@ -96,7 +96,8 @@ def build_programs(nvcc: str | None = None, verbose: bool = False) -> list[Path]
     built = []
     for src in sorted(NATIVE_SRC.glob("*.cpp")):
         exe = BIN_DIR / src.stem
-        newest = max(src.stat().st_mtime, LIB.stat().st_mtime, (ROOT / "include" / "gmt_b200.h").stat().st_mtime)
+        newest = max(src.stat().st_mtime, LIB.stat().st_mtime,
+                     *(h.stat().st_mtime for h in (ROOT / "include").glob("*.h*")))
         if not exe.exists() or exe.stat().st_mtime < newest:
             cmd = [nvcc, "-O2", "-std=c++17", "-I", str(ROOT / "include"), str(src), "-o", str(exe),
                    "-L", str(OUT_DIR), "-lgmt_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/..", "-lcudart"]

@@ -15,7 +15,23 @@ def base_parser(description: str) -> argparse.ArgumentParser:
     ap.add_argument("--impl", choices=["fused", "baseline"], default=None,
                     help="peer-memory kernels or the library-only restatement (default: fused on GPUs)")
     ap.add_argument("--cpu", action="store_true", help="force the CPU/gloo flavour")
+    ap.add_argument("--jsonl", default=None, metavar="PATH",
+                    help="append one machine-readable JSON record per rank to PATH (the printed lines stay as they are)")
     return ap
+
+
+# machine-readable twin of the printed lines: programs call record(key=value) next to their
+# printf-style output; finish() appends {"program", "rank", "world", "impl", ...} to --jsonl PATH
+_state = {"path": None, "program": None, "impl": None, "fields": {}}
+
+
+def record(**fields) -> None:
+    _state["fields"].update(fields)
+
+
+def record_append(key: str, item) -> None:
+    """For programs that print several result lines (one list entry per line)."""
+    _state["fields"].setdefault(key, []).append(item)
 
 
 def start(args) -> tuple:
@@ -33,11 +49,26 @@ def start(args) -> tuple:
     if impl == "fused" and not rt.is_cuda:
         out("fused kernels need a CUDA device; using the baseline (library-only) path")
         impl = "baseline"
+    _state.update(path=getattr(args, "jsonl", None) or os.environ.get("GMT_JSONL"), program=os.path.basename(sys.argv[0] or "").replace(".py", ""),
+                  impl=impl, fields={})
+    if _state["program"] in ("", "__main__"):
+        _state["program"] = (sys.modules["__main__"].__spec__.name.rsplit(".", 1)[-1]
+                             if getattr(sys.modules.get("__main__"), "__spec__", None) else "program")
     return rt, out, impl
 
 
 def finish(rt) -> None:
     sys.stdout.flush()
+    if _state["path"]:
+        import json
+        rec = {"program": _state["program"], "rank": rt.rank, "world": rt.world_size, "impl": _state["impl"],
+               "device": rt.device_id if rt.is_cuda else "cpu", **_state["fields"]}
+        line = json.dumps(rec) + "\n"
+        fd = os.open(_state["path"], os.O_WRONLY | os.O_CREAT | os.O_APPEND, 0o644)
+        try:
+            os.write(fd, line.encode())    # one write per record: lines of different ranks never interleave
+        finally:
+            os.close(fd)
     runtime.finalize()
 
 

@@ -94,9 +94,8 @@ def main(argv=None) -> int:
     out(report.time_line(r, W, "kernel", k_time))
     out(report.time_line(r, W, "barrier", b_time))
     out(report.time_line(r, W, "gather", g_time))
-    report.JsonlSink().write({"program": "mpi_daxpy_nvtx", "impl": impl, "rank": r, "world": W, "n": n,
-                              "managed": args.managed, "kernel_s": k_time, "gather_s": g_time,
-                              "gather_GBs_in": 2 * (W - 1) * n * 8 / g_time / 1e9 if g_time > 0 else None})
+    _common.record(n=n, managed=args.managed, sum=s, allsum=total, total_s=total_time, kernel_s=k_time, barrier_s=b_time,
+                   gather_s=g_time, gather_GBs_in=2 * (W - 1) * n * 8 / g_time / 1e9 if g_time > 0 else None)
     _common.finish(rt)
     return 0
 

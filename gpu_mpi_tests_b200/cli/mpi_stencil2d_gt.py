@@ -83,6 +83,9 @@ def test_deriv(rt, out, impl, space, dim, mem, use_buffers, n_local_deriv, n_oth
     err_sum = rt.reduce_scalar(err)
     if r == 0:
         out(report.test_deriv_line(dim, mem, use_buffers, time_sum, err_sum))
+    _common.record_append("tests", {"test": "deriv", "dim": dim, "space": mem, "buf": int(use_buffers), "n_iter": n_iter,
+                                    "exchange_s": total, "err_norm": err,
+                                    "exchange_s_sum": time_sum if r == 0 else None, "err_sum": err_sum if r == 0 else None})
     del wl
     if rt.is_cuda:
         torch.cuda.empty_cache()
@@ -130,6 +133,8 @@ def test_sum(rt, out, impl, space, dim, mem, n_local_deriv, n_other, n_iter, n_w
     time_sum = rt.reduce_scalar(total)
     if r == 0:
         out(report.test_sum_line(dim, mem, time_sum))
+    _common.record_append("tests", {"test": "sum", "dim": dim, "space": mem, "n_iter": n_iter, "allreduce_s": total,
+                                    "allreduce_s_sum": time_sum if r == 0 else None})
 
 
 def _main(argv=None) -> int:

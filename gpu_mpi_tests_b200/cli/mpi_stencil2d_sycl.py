@@ -108,6 +108,8 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
     ms = total / max(n_iter, 1) * 1000
     err = wl.err_norm(r)
     wl.check()
+    from . import _common as _c
+    _c.record(nx_local=nx_local, ny=ny, n_iter=n_iter, stage_host=bool(stage_host), exchange_ms=ms, err_norm=err)
     if line_style == "sycl":
         out(report.exchange_time_ms(r, W, ms))
         out(report.err_norm_line(r, W, rt.device_id, rt.vendor_id, err))

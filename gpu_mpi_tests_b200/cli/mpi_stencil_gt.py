@@ -51,6 +51,7 @@ def _main(argv=None) -> int:
     err = wl.err_norm(r)
     wl.check()
     out(report.err_norm_line(r, rt.world_size, rt.device_id, rt.vendor_id, err))
+    _common.record(n_global=n_global, n_local=slab.n_local, exchange_s=seconds, err_norm=err)
     _common.finish(rt)
     return 0
 

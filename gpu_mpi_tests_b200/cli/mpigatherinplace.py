@@ -29,6 +29,7 @@ def main(argv=None) -> int:
     lsum, asum = wl.sums(rt.rank)
     wl.check()
     out(report.gather_line(rt.rank, rt.world_size, lsum, asum))
+    _common.record(n=args.n, op="allgather" if args.gather is None else f"gather:{args.gather}", lsum=lsum, asum=asum)
     _common.finish(rt)
     return 0
 

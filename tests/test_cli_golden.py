@@ -147,6 +147,24 @@ def test_sycl_oo_debug_dumps_world2():
             assert recv[(j, i)] == pytest.approx(sent[j * 16 + i], abs=1e-6)
 
 
+def test_jsonl_records_world2(tmp_path):
+    """--jsonl PATH: one machine-readable record per rank next to the printed lines."""
+    import json
+    path = tmp_path / "rec.jsonl"
+    run_cli("mpi_stencil_gt", "--points", 4096, "--jsonl", path, nproc=2)
+    run_cli("mpi_stencil2d_gt", 16, 2, "--n-other", 32, "--jsonl", path, nproc=2)
+    recs = [json.loads(ln) for ln in path.read_text().splitlines()]
+    one_d = sorted((r for r in recs if r["program"] == "mpi_stencil_gt"), key=lambda r: r["rank"])
+    assert [r["rank"] for r in one_d] == [0, 1] and all(r["world"] == 2 and r["n_local"] == 2048 for r in one_d)
+    assert all(r["err_norm"] < 1e-3 and r["exchange_s"] >= 0 for r in one_d)
+    two_d = [r for r in recs if r["program"] == "mpi_stencil2d_gt"]
+    assert len(two_d) == 2
+    for r in two_d:
+        kinds = [(t["test"], t["dim"]) for t in r["tests"]]
+        assert kinds.count(("deriv", 0)) >= 2 and kinds.count(("deriv", 1)) >= 2 and ("sum", 0) in kinds and ("sum", 1) in kinds
+        assert all(t["err_norm"] < 1e-3 for t in r["tests"] if t["test"] == "deriv")
+
+
 def test_rank_device_ratio_error_exit1():
     lines = run_cli("mpi_daxpy", nproc=3, env_extra={"GMT_FAKE_DEVICES": "2"}, expect_rc=1)
     match_all(lines, [r"ERROR: Number of ranks \(3\) not a multiple of number of GPUs \(2\)"])

@@ -238,3 +238,19 @@ def test_native_stencil1d_program():
                          text=True, timeout=60)
     if W > 1:
         assert res.returncode == 1 and "must be divisor of domain size" in res.stdout
+
+
+@pytest.mark.parametrize("ranks", [1, 4])
+def test_native_daxpy_allreduce_program(ranks):
+    """Fused daxpy + global sum through the C++ conveniences (include/gmt_b200.hpp)."""
+    n_dev = torch.cuda.device_count()
+    if ranks > n_dev and ranks % n_dev:
+        pytest.skip("rank count does not divide")
+    exe = EXE.parent / "gmt_daxpy_allreduce"
+    n = 300000
+    res = subprocess.run([str(exe), "--n", str(n), "--ranks", str(ranks), "--iters", "20"], capture_output=True,
+                         text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    for r in range(ranks):
+        assert f"{r}/{ranks} ALLSUM = {ranks * (n + 1) / 2:f}" in res.stdout
+    assert re.search(r"[0-9.]+ us per call", res.stdout)
