@@ -42,14 +42,21 @@ def main():
         hdr, units = rows[0], rows[1]
         lines.append(f"## {rep.name}")
         lines.append("")
-        lines.append("| kernel | " + " | ".join(label for _m, label in WANT) + " | algorithmic GB/s |")
-        lines.append("|---|" + "---|" * (len(WANT) + 1))
-        seen = {}
+        lines.append("| kernel | " + " | ".join(label for _m, label in WANT) + " | algorithmic GB/s | top warp stalls (warps per issue) |")
+        lines.append("|---|" + "---|" * (len(WANT) + 2))
+        # one row per kernel (and grid size): the LAST capture, i.e. a warm launch
+        last = {}
         for r in rows[2:]:
-            name = r[hdr.index("Kernel Name")].split("(")[0].strip()
-            seen[name] = seen.get(name, 0) + 1
-            if seen[name] > 1:
-                continue
+            key = (r[hdr.index("Kernel Name")].split("(")[0].strip(), r[hdr.index("Grid Size")]
+                   if "Grid Size" in hdr else "")
+            last[key] = r
+        stall_cols = [(i, h[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")])
+                      for i, h in enumerate(hdr)
+                      if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")
+                      and "not_issued" not in h]
+        for (name, grid_dims), r in last.items():
+            if grid_dims.replace(" ", "").split(",")[1:2] not in ([], ["1"]):
+                name += f" grid {grid_dims}: {grid_dims.split(',')[1].strip()} virtual ranks, real exchange"
             cells = []
             vals = {}
             for metric, _label in WANT:
@@ -70,7 +77,14 @@ def main():
                 algo = f"{total / (float(dur) * tsc[du]) / 1e9:.0f} (DRAM bytes/time; {total / (float(dur) * tsc[du]) / 1e9 / hbm:.2f} of measured)"
             except Exception:  # noqa: BLE001
                 pass
-            lines.append(f"| `{name}` | " + " | ".join(cells) + f" | {algo} |")
+            stalls = []
+            for i, reason in stall_cols:
+                try:
+                    stalls.append((float(r[i]), reason))
+                except ValueError:
+                    pass
+            top = ", ".join(f"{reason} {v:.1f}" for v, reason in sorted(stalls, reverse=True)[:3]) or "-"
+            lines.append(f"| `{name}` | " + " | ".join(cells) + f" | {algo} | {top} |")
         lines.append("")
     (OUT / "ncu_summary.md").write_text("\n".join(lines) + "\n")
     print(OUT / "ncu_summary.md")

@@ -1,6 +1,10 @@
 #!/usr/bin/env python
 """Short single-GPU program for ncu: a few launches of each hot kernel at the BASELINE shapes.
-    python tools/profile_target.py [grid|dim0|dim1|1d|daxpy|all]"""
+    python tools/profile_target.py [grid|grid4|dim0|dim0x2|dim1|1d|daxpy|all]
+
+grid4 / dim0x2 run 4 (2x2) / 2 virtual ranks in ONE cooperative launch on this GPU, so the
+capture shows the fused kernel with its real exchange work (pushes into neighbours' inboxes,
+flag waits, ghost landing) -- a world of one has no neighbours."""
 import sys
 from pathlib import Path
 
@@ -15,7 +19,9 @@ what = sys.argv[1] if len(sys.argv) > 1 else "all"
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 space = VirtualSpace(1, dev)
-N = 3
+import os
+
+N = int(os.environ.get("PROFILE_N", "3"))
 if what in ("grid", "all"):
     p = FusedStencil2D(space, 1, 1, 16384, 16384, 2, 2, with_err=True)
     p.init_analytic()
@@ -23,6 +29,23 @@ if what in ("grid", "all"):
         p.step()
     torch.cuda.synchronize()
     print("grid err", p.err_norm(0))
+    del p
+if what in ("grid4", "all"):
+    p = FusedStencil2D(VirtualSpace(4, dev), 2, 2, 8192, 8192, 2, 2, with_err=True)
+    p.init_analytic(poison=1e30)
+    for _ in range(N):
+        p.step()
+    torch.cuda.synchronize()
+    p.check_status()
+    print("grid4 err", [p.err_norm(r) for r in range(4)])
+    del p
+if what in ("dim0x2", "all"):
+    p = FusedStencil2D(VirtualSpace(2, dev), 2, 1, 1024, 262144, 2, 0, with_err=False)
+    p.init_analytic(poison=1e30)
+    for _ in range(N):
+        p.step()
+    torch.cuda.synchronize()
+    p.check_status()
     del p
 if what in ("dim0", "all"):
     p = FusedStencil2D(space, 1, 1, 1024, 524288, 2, 0, with_err=False)
@@ -36,6 +59,9 @@ if what in ("dim1", "all"):
     p.init_analytic()
     for _ in range(N):
         p.step()
+    for v in ("vector", "tma"):      # plain one-shot kernel and the TMA cluster/multicast kernel
+        for _ in range(N):
+            local.stencil2d(p.z[0], 1, 1.0, out=p.out[0], variant=v)
     torch.cuda.synchronize()
     del p
 if what in ("1d", "all"):
