@@ -7,7 +7,7 @@ TORCHRUN = $(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node $(NP) --ma
 .PHONY: all build force test test-gpu bench sweep sass clean \
         daxpy daxpy_nvtx mpi_daxpy mpi_daxpy_nvtx_managed mpi_daxpy_nvtx_unmanaged mpi_daxpy_gt \
         mpi_stencil_gt mpi_stencil2d_gt mpi_stencil2d_sycl mpi_stencil2d_sycl_oo mpienv mpigatherinplace \
-        gmt_stencil2d gmt_daxpy
+        gmt_stencil2d gmt_stencil1d gmt_daxpy gmt_mpi_daxpy gmt_mpienv gmt_daxpy_gather gmt_daxpy_allreduce gmt_gatherinplace
 
 all: build
 
@@ -43,7 +43,7 @@ mpi_daxpy_nvtx_unmanaged:
 	$(TORCHRUN) -m gpu_mpi_tests_b200.cli.mpi_daxpy_nvtx $(ARGS)
 
 # native programs (C++ on the C ABI, no Python): one process drives every GPU of the node
-gmt_stencil2d gmt_daxpy: build
+gmt_stencil2d gmt_stencil1d gmt_daxpy gmt_mpi_daxpy gmt_mpienv gmt_daxpy_gather gmt_daxpy_allreduce gmt_gatherinplace: build
 	gpu_mpi_tests_b200/_native/bin/$@ $(ARGS)
 
 clean:

@@ -274,3 +274,38 @@ def test_native_engine_device_rule():
             assert NativeEngine2D.default_device(n_ranks, r, n_dev) == map_rank_to_device(n_ranks, r, n_dev)[0]
     with pytest.raises(GmtError, match="not a multiple"):
         NativeEngine2D.default_device(9, 0, 8)
+
+
+def test_check_header_overloads_compile(tmp_path):
+    """include/gmt_check.hpp: CHECK/WARN for gmt codes and cudaError_t, and the compile-out switch
+    (the reference's GPU_NO_CHECK_CALLS, cuda_error.h:16-26) -- compile-only, no GPU needed."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not Path(nvcc).exists():
+        pytest.skip("nvcc not found")
+    src = tmp_path / "t.cpp"
+    src.write_text('#include <cuda_runtime_api.h>\n#include "gmt_check.hpp"\n#include "gmt_b200.hpp"\n'
+                   'int f(double* p) {\n  GMT_CHECK("gmt call", gmt_set_device(0));\n'
+                   '  int w = GMT_WARN("cuda call", cudaSetDevice(0));\n  GMT_PTRINFO(p);\n  GMT_MEMINFO(p, 8);\n'
+                   '  gmt::NvtxRange r("x");\n  return w;\n}\n')
+    inc = str(Path(__file__).resolve().parents[1] / "include")
+    for extra in ([], ["-DGMT_NO_CHECK_CALLS"]):
+        res = subprocess.run([nvcc, "-std=c++17", "-I", inc, *extra, "-c", str(src), "-o", str(tmp_path / "t.o")],
+                             capture_output=True, text=True)
+        assert res.returncode == 0, res.stderr
+
+
+def test_native_mpienv_program():
+    """native/gmt_mpienv.cpp needs no GPU: same line as cli.mpienv (mpienv.f90:32)."""
+    import os
+    import subprocess
+    from pathlib import Path
+    from gpu_mpi_tests_b200.utils import report
+    exe = Path(__file__).resolve().parents[1] / "gpu_mpi_tests_b200" / "_native" / "bin" / "gmt_mpienv"
+    if not exe.exists():
+        pytest.skip("native programs not built")
+    res = subprocess.run([str(exe), "--ranks", "3"], capture_output=True, text=True, env=dict(os.environ, MEMORY_PER_CORE="12"))
+    assert res.returncode == 0
+    assert res.stdout.splitlines() == [report.mpienv_line(r, 12) for r in range(3)]

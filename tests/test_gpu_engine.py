@@ -263,3 +263,27 @@ def test_native_daxpy_allreduce_program(ranks):
     for r in range(ranks):
         assert f"{r}/{ranks} ALLSUM = {ranks * (n + 1) / 2:f}" in res.stdout
     assert re.search(r"[0-9.]+ us per call", res.stdout)
+
+
+def test_native_mpi_daxpy_program():
+    """mpi_daxpy's contract (mpi_daxpy.cc:36-62,101-157): rank->device lines (1-based, memory share),
+    MEMORY_PER_CORE echo, preferred-location report for device/managed/host pointers, SUM per rank."""
+    import os
+    exe = EXE.parent / "gmt_mpi_daxpy"
+    n_dev = torch.cuda.device_count()
+    ranks = 2 * n_dev
+    env = dict(os.environ, MEMORY_PER_CORE="42")
+    res = subprocess.run([str(exe), "--ranks", str(ranks)], capture_output=True, text=True, timeout=120, env=env)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = res.stdout
+    assert "MEMORY_PER_CORE=42" in out
+    for r in range(ranks):
+        assert re.search(rf"^RANK\[{r + 1}/{ranks}\] => DEVICE\[{r // 2 + 1}/{n_dev}\] mem=\d+$", out, re.M)
+        assert f"{r}/{ranks} SUM = 524800.000000" in out
+    assert "CUDA PreferredLocation of 'd_x' is UNMANAGED" in out
+    assert re.search(r"CUDA PreferredLocation of 'm_x' is (CPU|DEVICE|INVALID) \(-?\d+\)", out)
+    assert "CUDA PreferredLocation of 'x' is NOT CUDA" in out
+    assert re.search(r"CUDA pointer d_x \([0-9a-f]+\): Device", out) and re.search(r"CUDA pointer m_x \([0-9a-f]+\): Managed", out)
+    if n_dev > 1:
+        res = subprocess.run([str(exe), "--ranks", str(n_dev + 1)], capture_output=True, text=True, timeout=60)
+        assert res.returncode == 1 and "not a multiple of number of GPUs" in res.stdout
