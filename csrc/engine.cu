@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <memory>
 #include <vector>
 
 #include "common.cuh"
@@ -51,6 +52,7 @@ struct gmt_engine2d {
   double dx = 0, dy = 0, sx = 0, sy = 0;
   std::vector<RankMem> ranks;
   std::vector<DeviceGroup> groups;
+  std::unique_ptr<gmt::DeviceExecutor> exec;   // one launching thread per GPU
 };
 
 namespace {
@@ -70,6 +72,7 @@ using gmt::take;
 
 int free_all(gmt_engine2d* e)
 {
+  e->exec.reset();
   for (auto& g : e->groups) {
     if (cudaSetDevice(g.device) != cudaSuccess) continue;
     if (g.stream) cudaStreamSynchronize(g.stream);
@@ -230,6 +233,11 @@ int gmt_engine2d_create(int px, int py, const int* devices, int64_t nx, int64_t 
     if (ce == cudaSuccess) ce = cudaEventCreate(&g.ev1);
     if (ce != cudaSuccess) return bail(gmt::cuda_fail(ce, "engine group set-up", __FILE__, __LINE__));
   }
+  {
+    std::vector<int> devs;
+    for (auto& g : e->groups) devs.push_back(g.device);
+    e->exec.reset(new gmt::DeviceExecutor(devs));
+  }
   *out = e;
   return 0;
 }
@@ -286,14 +294,13 @@ int gmt_engine2d_step(gmt_engine2d* e)
 {
   DeviceRestore restore_;
   GMT_REQUIRE(e, GMT_EINVAL, "gmt_engine2d_step: NULL engine");
-  // launches are asynchronous: by the time a device's kernel polls a neighbour's flag, the
-  // neighbour's launch has been issued a few microseconds later by this same loop
-  for (auto& g : e->groups) {
-    GMT_CUDA(cudaSetDevice(g.device));
-    const int rc = gmt_fused_stencil2d_f64(g.desc, (int)g.ranks.size(), e->nx, e->ny, e->gx, e->gy, e->with_err,
-                                           g.stream);
-    if (rc) return rc;
-  }
+  // one launch per GPU, issued by that GPU's worker thread so that all GPUs start together; the
+  // launches are asynchronous and the kernels' flag protocol orders everything else
+  const int rc = e->exec->run([e](int i) {
+    DeviceGroup& g = e->groups[i];
+    return gmt_fused_stencil2d_f64(g.desc, (int)g.ranks.size(), e->nx, e->ny, e->gx, e->gy, e->with_err, g.stream);
+  });
+  if (rc) return rc;
   ++e->steps;
   return 0;
 }

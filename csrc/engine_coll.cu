@@ -11,6 +11,7 @@
 // multicast variants stay with the torch symmetric-memory path (parallel/collectives.py).
 #include <algorithm>
 #include <cstring>
+#include <memory>
 #include <vector>
 
 #include "common.cuh"
@@ -45,12 +46,14 @@ struct gmt_coll_engine {
   std::vector<CollRankMem> ranks;
   std::vector<CollGroup> groups;
   std::vector<int> group_of, slot_of;   // rank -> group index, index inside the group
+  std::unique_ptr<gmt::DeviceExecutor> exec;   // one launching thread per GPU
 };
 
 namespace {
 
 int free_all(gmt_coll_engine* e)
 {
+  e->exec.reset();
   for (auto& g : e->groups) {
     if (cudaSetDevice(g.device) != cudaSuccess) continue;
     if (g.stream) cudaStreamSynchronize(g.stream);
@@ -70,17 +73,12 @@ int free_all(gmt_coll_engine* e)
   return 0;
 }
 
-// run `launch(group)` on every device; the launches are asynchronous, so the kernels of all GPUs
-// are in flight together although one host thread issues them
+// run `launch(group)` on every device at once (DeviceExecutor: the GPU's worker thread issues it, so
+// the GPUs start together instead of 4-5 us apart); the launches themselves are asynchronous
 template <class F>
 int for_each_group(gmt_coll_engine* e, F&& launch)
 {
-  for (auto& g : e->groups) {
-    GMT_CUDA(cudaSetDevice(g.device));
-    const int rc = launch(g);
-    if (rc) return rc;
-  }
-  return 0;
+  return e->exec->run([&](int i) { return launch(e->groups[i]); });
 }
 
 }  // namespace
@@ -190,6 +188,11 @@ int gmt_coll_engine_create(int world, const int* devices, int64_t buf_doubles, i
     if (ce == cudaSuccess) ce = cudaEventCreate(&g.ev0);
     if (ce == cudaSuccess) ce = cudaEventCreate(&g.ev1);
     if (ce != cudaSuccess) return bail(gmt::cuda_fail(ce, "collective engine group set-up", __FILE__, __LINE__));
+  }
+  {
+    std::vector<int> devs;
+    for (auto& g : e->groups) devs.push_back(g.device);
+    e->exec.reset(new gmt::DeviceExecutor(devs));
   }
   *out = e;
   return 0;
@@ -346,15 +349,14 @@ int gmt_coll_engine_elapsed_ms(gmt_coll_engine* e, double* ms)
 {
   DeviceRestore restore_;
   GMT_REQUIRE(e && ms, GMT_EINVAL, "gmt_coll_engine_elapsed_ms: bad arguments");
-  float worst = 0.f;
-  const int rc = for_each_group(e, [&](CollGroup& g) {
-    float t = 0.f;
+  std::vector<float> t(e->groups.size(), 0.f);   // one slot per GPU: the workers run concurrently
+  const int rc = e->exec->run([&](int i) {
+    CollGroup& g = e->groups[i];
     GMT_CUDA(cudaEventSynchronize(g.ev1));
-    GMT_CUDA(cudaEventElapsedTime(&t, g.ev0, g.ev1));
-    worst = std::max(worst, t);
+    GMT_CUDA(cudaEventElapsedTime(&t[i], g.ev0, g.ev1));
     return 0;
   });
-  *ms = worst;
+  *ms = t.empty() ? 0.0 : *std::max_element(t.begin(), t.end());
   return rc;
 }
 
