@@ -58,6 +58,8 @@ def main() -> int:
         return 0
 
     import torch
+    from gpu_mpi_tests_b200._native.build import ensure_built
+    ensure_built()   # a fresh checkout has no build outputs; no-op when the library is there
     from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
     from gpu_mpi_tests_b200.parallel import runtime
     from gpu_mpi_tests_b200.utils import timing

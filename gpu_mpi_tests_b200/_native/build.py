@@ -110,6 +110,24 @@ def build_programs(nvcc: str | None = None, verbose: bool = False) -> list[Path]
     return built
 
 
+def ensure_built() -> Path:
+    """Build the library and the programs if the tree has none (a fresh checkout: build outputs are
+    git-ignored).  Safe to call from every rank of a multi-process launch: an exclusive file lock
+    lets one process build while the others wait and then find the result."""
+    import fcntl
+    if LIB.exists():
+        return LIB
+    OUT_DIR.mkdir(parents=True, exist_ok=True)
+    with open(OUT_DIR / ".build.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not LIB.exists():
+                build()
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+    return LIB
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose=True)
     print(LIB)

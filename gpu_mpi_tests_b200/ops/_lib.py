@@ -191,8 +191,14 @@ class _Lib:
     def load(self):
         if self._dll is None:
             if not LIB_PATH.exists():
-                raise GmtError("load", -1, f"{LIB_PATH} not found: run `python -m gpu_mpi_tests_b200._native.build` "
-                               "(or __graft_entry__.build()) first")
+                # build outputs are git-ignored: a fresh checkout compiles them on first use (one process builds,
+                # the other ranks wait on a file lock); no compiler -> a loud error, never a fallback
+                try:
+                    from .._native.build import ensure_built
+                    ensure_built()
+                except Exception as exc:  # noqa: BLE001
+                    raise GmtError("load", -1, f"{LIB_PATH} not found and building it failed ({exc}); run "
+                                   "`python -m gpu_mpi_tests_b200._native.build` (or __graft_entry__.build())") from exc
             self._dll = C.CDLL(str(LIB_PATH), mode=C.RTLD_GLOBAL)
             self._dll.gmt_last_error.restype = C.c_char_p
         return self._dll
