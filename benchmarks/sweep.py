@@ -188,7 +188,7 @@ def collectives(rt, space, args):
     for n in (1024, 1 << 14, 1 << 18):
         pc = PeerCollectives(space, stage_cap=n)
         v = torch.ones(n, dtype=F64, device=dev) * 1e-12
-        algos = ["one_shot", "two_shot"] + (["multimem"] if pc.has_multicast else [])
+        algos = ["ll", "one_shot", "two_shot"] + (["multimem"] if pc.has_multicast else [])
         for algo in algos:
             ms, how = graph_ms(lambda: pc.allreduce({r: v}, algo=algo), 50, 10, dev)
             emit(rt, {"config": "allreduce_inplace", "impl": f"fused_{algo}", "n_gpus": W, "bytes": n * 8, "us": ms * 1e3,

@@ -24,6 +24,7 @@ namespace gmt {
 constexpr int kCollThreads = 512;
 constexpr int kRoundStride = 32;  // words per signalling round in a flag block
 constexpr int kLLBase = 64;       // LL slots: [parity][src rank][2 words] after the two rounds
+constexpr int64_t kLLMaxDoubles = 32768;  // vectors up to 256 KiB travel as LL cells by default
 
 struct CollShared {
   gmt_coll_rank R;
@@ -245,6 +246,63 @@ __device__ __forceinline__ void reduce_tail(CollShared& S, uint64_t e, int64_t n
   if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
 }
 
+// ---- "LL" all-reduce: no grid-wide rendezvous, no flag round trip.  Every rank stores each of its
+// values as an LL cell into the slot [parity][its rank][i] of EVERY rank (its own included), then
+// sums, in rank order, the W cells of each i as they turn up.  The cells live behind the four
+// staging vectors: word index 4*cap + ((parity*W + src)*cap + i)*2 of a rank's staging area.
+// Parity double-buffering is enough for the same reason as for the halo inboxes: a rank can only be
+// two calls ahead of a peer after that peer has read everything of the call in between.
+__device__ __forceinline__ uint64_t* ll_cell(const CollShared& S, int owner, int par, int src, int64_t i)
+{
+  return reinterpret_cast<uint64_t*>(S.stage[owner]) + 4 * S.R.stage_cap +
+         (((int64_t)par * S.R.world + src) * S.R.stage_cap + i) * 2;
+}
+__device__ __forceinline__ void ll_push(const CollShared& S, uint64_t e, int64_t i, double v)
+{
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
+  for (int k = 0; k < W; ++k) st_ll_cell(ll_cell(S, (r + k) % W, par, r, i), v, e & 0xffffffffull);
+}
+__device__ __forceinline__ double ll_collect(CollShared& S, uint64_t e, int64_t i)
+{
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
+  const int64_t limit = S.R.spin_limit > 0 ? S.R.spin_limit : kDefaultSpinLimit;
+  double s = 0.0;
+  for (int src = 0; src < W; ++src) {   // rank order: identical bits on every rank
+    const uint64_t* cell = ll_cell(S, r, par, src, i);
+    double v = 0.0;
+    bool ok = false;
+    for (int64_t it = 0; it < limit; ++it) {
+      if (ld_ll_cell(cell, e & 0xffffffffull, v)) {
+        ok = true;
+        break;
+      }
+      if (it > 64) __nanosleep(32);
+    }
+    if (!ok) atomicExch(S.R.status, 1u + src);
+    s += v;
+  }
+  return s;
+}
+// every thread collects the indices of its grid-stride share; then the epoch advances
+__device__ __forceinline__ void ll_tail(CollShared& S, uint64_t e, int64_t n)
+{
+  double* out = S.R.out;
+  const int64_t stride = (int64_t)gridDim.x * kCollThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += stride) out[i] = ll_collect(S, e, i);
+  if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
+}
+
+__global__ void __launch_bounds__(kCollThreads, 2)
+  allreduce_ll_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  const double* in = S.R.in;
+  const int64_t stride = (int64_t)gridDim.x * kCollThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += stride) ll_push(S, e, i, in[i]);
+  ll_tail(S, e, n);
+}
+
 template <int kAlgo>
 __global__ void __launch_bounds__(kCollThreads, 2)
   allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n)
@@ -284,7 +342,10 @@ __global__ void __launch_bounds__(kCollThreads, 2)
       }
       if (i < nx) a0 += col[i];
       const double s = warp_sum(a0 + a1);
-      if (lane == 0) mine[j] = s;
+      if (lane == 0) {
+        if (kAlgo == 3) ll_push(S, e, j, s);
+        else mine[j] = s;
+      }
     }
   } else {
     // out[i] = sum_j z(i,j): 32 rows per CTA trip, the 16 warps split the columns
@@ -299,13 +360,20 @@ __global__ void __launch_bounds__(kCollThreads, 2)
         double s = 0.0;
 #pragma unroll
         for (int k = 0; k < kCollThreads / 32; ++k) s += tile[k][lane];
-        mine[i] = s;
+        if (kAlgo == 3) ll_push(S, e, i, s);
+        else mine[i] = s;
       }
       __syncthreads();
     }
   }
+  if (kAlgo == 3) {
+    // the sums went out as LL cells the moment they were known; collecting needs no rendezvous
+    // (all CTAs of the grid are resident, so spinning on a cell a sibling CTA has yet to push is safe)
+    ll_tail(S, e, n_out);
+    return;
+  }
   publish_inputs(S, e);
-  reduce_tail<kAlgo>(S, e, n_out);
+  reduce_tail<kAlgo == 3 ? 0 : kAlgo>(S, e, n_out);
 }
 
 // ============================================================ daxpy + global sum
@@ -477,11 +545,15 @@ int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, in
 {
   using namespace gmt;
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_allreduce_f64: bad argument");
-  GMT_REQUIRE(algo >= 0 && algo <= 2, GMT_EINVAL, "gmt_allreduce_f64: unknown algorithm %d", algo);
-  const void* k = algo == 0 ? (const void*)allreduce_kernel<0>
-                 : algo == 1 ? (const void*)allreduce_kernel<1> : (const void*)allreduce_kernel<2>;
+  GMT_REQUIRE(algo >= 0 && algo <= 3, GMT_EINVAL, "gmt_allreduce_f64: unknown algorithm %d", algo);
+  const void* k = algo == 0   ? (const void*)allreduce_kernel<0>
+                  : algo == 1 ? (const void*)allreduce_kernel<1>
+                  : algo == 2 ? (const void*)allreduce_kernel<2>
+                              : (const void*)allreduce_ll_kernel;
   int grid = 0;
-  int rc = coll_grid(k, (n + kCollThreads * 4 - 1) / (kCollThreads * 4), n_ranks, &grid);
+  // LL needs no grid-wide rendezvous, so it can afford one element per thread; the others keep few CTAs
+  const int64_t per_cta = algo == 3 ? kCollThreads : kCollThreads * 4;
+  int rc = coll_grid(k, std::min<int64_t>((n + per_cta - 1) / per_cta, 64), n_ranks, &grid);
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&n};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));
@@ -508,7 +580,9 @@ int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int6
   GMT_REQUIRE(axis == 0 || axis == 1, GMT_EINVAL, "gmt_axis_sum_allreduce_f64: axis must be 0 or 1");
   GMT_REQUIRE(n_out >= 0 && n_out <= (axis == 0 ? ny : nx), GMT_EINVAL,
               "gmt_axis_sum_allreduce_f64: n_out exceeds the surviving extent");
-  const void* k = (const void*)axis_sum_allreduce_kernel<0>;
+  // LL cells (16 bytes per double per peer) while the vector is small, one-shot beyond
+  const void* k = n_out <= kLLMaxDoubles ? (const void*)axis_sum_allreduce_kernel<3>
+                                         : (const void*)axis_sum_allreduce_kernel<0>;
   int grid = 0;
   const int64_t work = axis == 0 ? (n_out + kCollThreads / 32 - 1) / (kCollThreads / 32) : (n_out + 31) / 32;
   int rc = coll_grid(k, work, n_ranks, &grid);

@@ -143,7 +143,7 @@ int gmt_coll_engine_create(int world, const int* devices, int64_t buf_doubles, i
   for (int r = 0; r < world; ++r) {
     CollRankMem& m = e->ranks[r];
     size_t cur = 0;
-    m.off_stage = take(cur, size_t(4) * e->stage_cap * 8);
+    m.off_stage = take(cur, size_t(4 + 4 * world) * e->stage_cap * 8);   // vectors + LL cells
     m.off_flags = take(cur, size_t(GMT_COLL_FLAG_WORDS) * 8);
     m.off_epoch = take(cur, 64), m.off_done = take(cur, 64), m.off_status = take(cur, 64);
     m.off_scratch = take(cur, scratch_bytes);
@@ -273,7 +273,8 @@ int gmt_coll_engine_gather(gmt_coll_engine* e, int64_t n, int root)
 int gmt_coll_engine_allreduce(gmt_coll_engine* e, int64_t n, int algo)
 {
   DeviceRestore restore_;
-  GMT_REQUIRE(e && (algo == 0 || algo == 1), GMT_EINVAL, "gmt_coll_engine_allreduce: algo must be 0 or 1");
+  GMT_REQUIRE(e && (algo == 0 || algo == 1 || algo == 3), GMT_EINVAL,
+              "gmt_coll_engine_allreduce: algo must be 0, 1 or 3 (2 needs NVLS multicast)");
   GMT_REQUIRE(n >= 0 && n <= e->stage_cap, GMT_ETOOBIG, "all-reduce of %lld doubles exceeds the staging capacity %lld",
               (long long)n, (long long)e->stage_cap);
   return for_each_group(e, [&](CollGroup& g) { return gmt_allreduce_f64(g.desc, (int)g.ranks.size(), n, algo, g.stream); });

@@ -69,6 +69,24 @@ __device__ __forceinline__ void multimem_red_add_f64(double* mc, double v)
   asm volatile("multimem.red.relaxed.sys.global.add.f64 [%0], %1;" ::"l"(mc), "d"(v) : "memory");
 }
 
+// "LL" cells: 16 bytes carry one double as two 8-byte words, each = 32 payload bits + the 32-bit
+// epoch.  8-byte stores are single-copy atomic, so a reader that sees the epoch in BOTH words has
+// the whole value: data and flag travel together, no fence, no separate flag store.
+__device__ __forceinline__ void st_ll_cell(uint64_t* cell, double v, uint64_t e32)
+{
+  const uint64_t bits = (uint64_t)__double_as_longlong(v);
+  const uint64_t w0 = (bits & 0xffffffffull) | (e32 << 32), w1 = (bits >> 32) | (e32 << 32);
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1,%2};" ::"l"(cell), "l"(w0), "l"(w1) : "memory");
+}
+__device__ __forceinline__ bool ld_ll_cell(const uint64_t* cell, uint64_t e32, double& v)
+{
+  uint64_t w0, w1;
+  asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(cell) : "memory");
+  if ((w0 >> 32) != e32 || (w1 >> 32) != e32) return false;
+  v = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+  return true;
+}
+
 constexpr int64_t kDefaultSpinLimit = 1LL << 28;  // ~ tens of seconds of polling
 
 // Bounded spin until *flag >= want.  Returns false on expiry (dead / never-launched

@@ -40,7 +40,7 @@ class PeerCollectives:
         self.buf_doubles, self.stage_cap = int(buf_doubles), max(int(stage_cap), 8)
         self.spin_limit = int(spin_limit)
         self._buf = space.alloc(max(self.buf_doubles, 4) * 8)
-        self._stage = space.alloc(4 * self.stage_cap * 8)
+        self._stage = space.alloc((4 + 4 * space.world) * self.stage_cap * 8)   # vectors + LL cells, zeroed
         self._flags = space.alloc(FLAG_WORDS * 8)
         n = len(self.ranks)
         self._epoch = torch.zeros(n, 8, dtype=torch.int64, device=self.device)
@@ -129,12 +129,17 @@ class PeerCollectives:
         if n * self.world > self.buf_doubles:
             raise ValueError(f"buffer of {self.buf_doubles} doubles cannot hold {self.world} slices of {n}")
 
-    ALGOS = {"one_shot": 0, "two_shot": 1, "multimem": 2}
+    ALGOS = {"one_shot": 0, "two_shot": 1, "multimem": 2, "ll": 3}
+    LL_MAX = 32768   # doubles: beyond this the 16-byte-per-double-per-peer cells stop paying
 
-    def allreduce(self, vec: dict, out: dict | None = None, algo: str = "one_shot") -> None:
-        """out[r] <- sum over ranks of vec[r]; in place when out is None."""
+    def allreduce(self, vec: dict, out: dict | None = None, algo: str = "auto") -> None:
+        """out[r] <- sum over ranks of vec[r]; in place when out is None.  algo: "ll" (epoch-carrying
+        16-byte cells, no rendezvous), "one_shot", "two_shot", "multimem"; "auto" = ll up to LL_MAX
+        doubles, two_shot beyond 2^17 doubles on 8+ ranks, else one_shot."""
         out = out or vec
         n = next(iter(vec.values())).numel()
+        if algo == "auto":
+            algo = "ll" if n <= self.LL_MAX else ("two_shot" if (n > (1 << 17) and self.world >= 8) else "one_shot")
         if n > self.stage_cap:
             raise ValueError(f"all-reduce of {n} doubles exceeds the staging capacity {self.stage_cap}")
         if algo == "multimem" and not self.has_multicast:

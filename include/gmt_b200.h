@@ -287,8 +287,9 @@ typedef struct {
   int32_t rank, world;
   double** peer_buf;      /* device array [world]: each rank's symmetric USER buffer (allgather/gather) */
   double* mc_buf;         /* NVLS multicast address of that buffer, or NULL */
-  double** peer_stage;    /* device array [world]: each rank's staging area, 4*stage_cap doubles:
-                             inputs [parity][stage_cap] then results [parity][stage_cap] */
+  double** peer_stage;    /* device array [world]: each rank's ZERO-INITIALISED staging area of
+                             (4 + 4*world)*stage_cap doubles: inputs [parity][stage_cap], results
+                             [parity][stage_cap], then the "LL" cells [parity][src rank][stage_cap] of 16 bytes */
   double* mc_stage;       /* multicast address of the staging area, or NULL */
   int64_t stage_cap;
   uint64_t** peer_flag;   /* device array [world]: each rank's flag block */
@@ -314,8 +315,11 @@ int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int r
 /* sum all-reduce of n doubles: out <- sum over ranks of in; out may alias in
  * (MPI_Allreduce(MPI_IN_PLACE), mpi_stencil2d_gt.cc:615,624).  n <= stage_cap.
  * algo: 0 one-shot (every rank reads every peer's vector), 1 two-shot (reduce-scatter then
- * allgather by peer stores), 2 one-shot through NVLS multimem.ld_reduce (needs mc_stage).
- * Ranks add in rank order, so every rank gets the same bits (algos 0 and 1).            */
+ * allgather by peer stores), 2 one-shot through NVLS multimem.ld_reduce (needs mc_stage),
+ * 3 "LL": every value is stored into every rank's staging area as a 16-byte cell that carries
+ * the epoch in both of its 8-byte words (data and flag arrive together: no fence, no flag round
+ * trip, no grid-wide rendezvous) -- the fastest up to a few hundred KiB.
+ * Ranks add in rank order, so every rank gets the same bits (algos 0, 1 and 3).          */
 int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int algo, gmt_stream_t stream);
 /* fused daxpy + global sum: y <- a*in + y on each rank, every rank's *out <- sum over all ranks
  * of sum(y_new)  (cublasDaxpy + MPI_Allgather + host sums, mpi_daxpy_nvtx.cc:245-310, in one kernel) */

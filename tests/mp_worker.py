@@ -104,7 +104,7 @@ def case_collectives(rt, args):
     if r == 0:
         for p in range(W):
             assert float(b[p * n]) == p + 1 and float(b[(p + 1) * n - 1]) == p + 1
-    algos = ["one_shot", "two_shot"] + (["multimem"] if pc.has_multicast else [])
+    algos = ["ll", "one_shot", "two_shot"] + (["multimem"] if pc.has_multicast else [])
     for algo in algos:
         for m in (1, 1024, 1 << 16):
             for it in range(3):

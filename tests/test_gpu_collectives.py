@@ -56,7 +56,7 @@ def test_allgather_from_separate_source(dev):
         assert torch.equal(pc.buffer(r), ref)
 
 
-@pytest.mark.parametrize("algo", ["one_shot", "two_shot"])
+@pytest.mark.parametrize("algo", ["ll", "one_shot", "two_shot"])
 @pytest.mark.parametrize("world,n", [(2, 1024), (8, 1024), (4, 1), (3, 4097), (8, 1 << 17)])
 def test_allreduce(dev, algo, world, n):
     pc = PeerCollectives(VirtualSpace(world, dev), stage_cap=max(n, 8), spin_limit=1 << 24)

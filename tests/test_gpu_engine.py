@@ -170,7 +170,7 @@ def test_native_collectives(world):
     # all-reduce (both algorithms), identical bits on every rank
     vecs = [torch.randn(1024, dtype=torch.float64, generator=gen) for _ in range(world)]
     total = torch.stack(vecs).sum(0)
-    for algo in (0, 1):
+    for algo in (0, 1, 3):
         ins = [v.to(d) for v, d in zip(vecs, devs)]
         outs = [torch.zeros(1024, dtype=torch.float64, device=d) for d in devs]
         for r in range(world):
