@@ -8,7 +8,7 @@ may be a whole launch ahead of its neighbour -- and `compute-sanitizer` cannot s
 sequential program of ATOMIC actions on shared words, and `explore()` walks every reachable
 interleaving, failing on the first assertion a schedule can break.
 
-Two models, matching csrc/stencil_fused.cu and csrc/collectives.cu:
+Three models, matching csrc/stencil_fused.cu and csrc/collectives.cu:
 
 * `halo_model(n_ranks, steps, buffers)`: per step e a rank stores its boundary into each
   neighbour's inbox[e % buffers], publishes e in the neighbour's flag (release), waits until its
@@ -19,6 +19,9 @@ Two models, matching csrc/stencil_fused.cu and csrc/collectives.cu:
   reading the previous result out of its buffer until it enters the next call, so peers may only
   store into it after it has signalled "entered" (round 0); round 1 signals "my stores are
   done".  Without the entry round the checker finds the overwritten read.
+
+* `ll_allreduce_model(n_ranks, calls, buffers)`: the LL-cell all-reduce, whose cells are matched by
+  EQUALITY with the epoch; two cell sets alternating by parity are enough, one is not (deadlock).
 
 Memory ordering is not modelled (actions are sequentially consistent); the mapping of "store
 data, then publish" onto `fence.acq_rel.sys` + `st.release.sys` / `ld.acquire.sys` is argued in
@@ -175,6 +178,40 @@ def allgather_model(n_ranks: int = 2, calls: int = 2, entry_round: bool = True):
                     got = mem[idx_buf(r, slot)]
                     assert got == (slot, c), f"rank {r} call {c}: slot {slot} holds {got}, expected {(slot, c)}"
                 prog.append((f"use{c}[{slot}]", use))
+        programs.append(prog)
+    return W, init, programs
+
+
+# ---------------------------------------------------------------------------- LL-cell all-reduce
+def ll_allreduce_model(n_ranks: int = 2, calls: int = 3, buffers: int = 2):
+    """Every rank stores its value, tagged with the call number, into cell[c % buffers][its rank] of
+    EVERY rank (one atomic store: data and epoch travel together), then takes the W cells of its own
+    area one by one, each as soon as its tag EQUALS the call number (not >=: a newer tag would mean
+    the value of this call is gone, and the wait would never end -- the checker reports that as a
+    deadlock)."""
+    W = n_ranks
+
+    def idx(owner, b, src):
+        return (owner * buffers + b) * W + src
+
+    init = tuple([None] * (W * buffers * W))
+    programs = []
+    for r in range(W):
+        prog = []
+        for c in range(1, calls + 1):
+            for k in range(W):
+                def push(mem, p, q=(r + k) % W, r=r, c=c):
+                    mem[idx(q, c % buffers, r)] = (r, c)
+                prog.append((f"push{c}->{(r + k) % W}", push))
+            for src in range(W):
+                def take_cell(mem, p, src=src, r=r, c=c):
+                    got = mem[idx(r, c % buffers, src)]
+                    if got is None or got[1] < c:
+                        return False          # not there yet
+                    if got[1] > c:
+                        return False          # overwritten by a later call: this wait can never end
+                    assert got == (src, c)
+                prog.append((f"take{c}[{src}]", take_cell))
         programs.append(prog)
     return W, init, programs
 

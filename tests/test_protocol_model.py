@@ -3,7 +3,8 @@
 ones: they show the checker can see the race each design element exists to prevent."""
 import pytest
 
-from gpu_mpi_tests_b200.utils.protocol_model import ProtocolViolation, allgather_model, check, halo_model
+from gpu_mpi_tests_b200.utils.protocol_model import (ProtocolViolation, allgather_model, check, halo_model,
+                                                      ll_allreduce_model)
 
 
 @pytest.mark.parametrize("n_ranks,steps", [(2, 4), (3, 3)])
@@ -32,6 +33,18 @@ def test_inplace_allgather_without_entry_round_races():
     with pytest.raises(ProtocolViolation, match="holds") as info:
         check(allgather_model, n_ranks=2, calls=2, entry_round=False)
     assert any(a.startswith("store2") for _r, a in info.value.trace)
+
+
+@pytest.mark.parametrize("n_ranks,calls", [(2, 4), (3, 3)])
+def test_ll_allreduce_with_two_cell_sets_is_safe(n_ranks, calls):
+    assert check(ll_allreduce_model, n_ranks=n_ranks, calls=calls, buffers=2) > 50
+
+
+def test_ll_allreduce_single_cell_set_loses_values():
+    """With one cell set a rank that is a call ahead replaces a value its peer has not taken yet;
+    cells are matched by equality with the epoch, so the peer's wait can never end."""
+    with pytest.raises(ProtocolViolation, match="deadlock"):
+        check(ll_allreduce_model, n_ranks=2, calls=2, buffers=1)
 
 
 def test_checker_reports_deadlock():
