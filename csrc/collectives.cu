@@ -186,19 +186,14 @@ __global__ void __launch_bounds__(kCollThreads, 2)
       own[i] = S.R.in[i];
   }
   // round 1: my slice has landed everywhere; return only when everyone's slice has landed here
+  // (a gather to root ends with the same all-to-all round although only the root needs the data:
+  // every collective here must leave nobody more than one call behind, because the staging areas and
+  // LL cells of the reductions are double-buffered by epoch parity -- a sender that could run through
+  // gathers without waiting for anybody would reach the same parity again while a slow rank is still
+  // reading what the sender put there two calls ago)
   if (arrive_last(S, S.R.done + 0)) {
-    if (all) {
-      signal_all(S, 1, e);
-      wait_all(S, 1, e);
-    } else if (r != root) {
-      signal_one(S, root, 1, e);
-    } else {
-      if ((int)threadIdx.x < W && (int)threadIdx.x != root) {
-        if (!wait_flag_ge(S.flag[r] + kRoundStride + threadIdx.x, e, S.R.spin_limit))
-          atomicExch(S.R.status, 1u + threadIdx.x);
-      }
-      __syncthreads();
-    }
+    signal_all(S, 1, e);
+    wait_all(S, 1, e);
     coll_finish(S, e);
   }
 }

@@ -22,6 +22,9 @@ Three models, matching csrc/stencil_fused.cu and csrc/collectives.cu:
 
 * `ll_allreduce_model(n_ranks, calls, buffers)`: the LL-cell all-reduce, whose cells are matched by
   EQUALITY with the epoch; two cell sets alternating by parity are enough, one is not (deadlock).
+  With `gather_between="nowait"` a gather whose senders wait for nobody sits between two
+  all-reduces and a fast sender laps a slow rank (deadlock again); `"barrier"` -- what
+  gmt_gather_f64 does: it ends with an all-to-all round -- is safe.
 
 Memory ordering is not modelled (actions are sequentially consistent); the mapping of "store
 data, then publish" onto `fence.acq_rel.sys` + `st.release.sys` / `ld.acquire.sys` is argued in
@@ -183,22 +186,41 @@ def allgather_model(n_ranks: int = 2, calls: int = 2, entry_round: bool = True):
 
 
 # ---------------------------------------------------------------------------- LL-cell all-reduce
-def ll_allreduce_model(n_ranks: int = 2, calls: int = 3, buffers: int = 2):
+def ll_allreduce_model(n_ranks: int = 2, calls: int = 3, buffers: int = 2, gather_between: str | None = None):
     """Every rank stores its value, tagged with the call number, into cell[c % buffers][its rank] of
     EVERY rank (one atomic store: data and epoch travel together), then takes the W cells of its own
     area one by one, each as soon as its tag EQUALS the call number (not >=: a newer tag would mean
     the value of this call is gone, and the wait would never end -- the checker reports that as a
     deadlock)."""
     W = n_ranks
+    n_cells = W * buffers * W
 
     def idx(owner, b, src):
         return (owner * buffers + b) * W + src
 
-    init = tuple([None] * (W * buffers * W))
+    def idx_sig(r, src):   # round-1 flag words of rank r
+        return n_cells + r * W + src
+
+    # gather_between: every even call is a gather to rank 0 instead of an all-reduce (the epoch, hence
+    # the parity of the NEXT all-reduce, still advances).  "nowait": senders signal the root and leave
+    # (what an MPI_Gather lets them do); "barrier": everybody signals everybody and waits for all.
+    init = tuple([None] * n_cells + [0] * (W * W))
     programs = []
     for r in range(W):
         prog = []
         for c in range(1, calls + 1):
+            if gather_between and c % 2 == 0:
+                targets = range(W) if gather_between == "barrier" else [0]
+                for q in targets:
+                    def sig(mem, p, q=q, r=r, c=c):
+                        mem[idx_sig(q, r)] = c
+                    prog.append((f"gsig{c}->{q}", sig))
+                if gather_between == "barrier" or r == 0:
+                    for q in range(W):
+                        def gwait(mem, p, q=q, r=r, c=c):
+                            return None if mem[idx_sig(r, q)] >= c else False
+                        prog.append((f"gwait{c}<-{q}", gwait))
+                continue
             for k in range(W):
                 def push(mem, p, q=(r + k) % W, r=r, c=c):
                     mem[idx(q, c % buffers, r)] = (r, c)

@@ -310,7 +310,9 @@ typedef struct {
  * use_multicast != 0: one multimem.st per 16 bytes through mc_buf instead of world-1 stores. */
 int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int from_in,
                       int use_multicast, gmt_stream_t stream);
-/* gather to root in place (MPI_Gather with MPI_IN_PLACE at the root, BASELINE config 5) */
+/* gather to root in place (MPI_Gather with MPI_IN_PLACE at the root, BASELINE config 5).  Ends with an
+ * all-to-all signalling round like every other collective here: no rank may get more than one call ahead
+ * of another, or the parity double-buffering of the reductions' staging areas would not hold. */
 int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int root, gmt_stream_t stream);
 /* sum all-reduce of n doubles: out <- sum over ranks of in; out may alias in
  * (MPI_Allreduce(MPI_IN_PLACE), mpi_stencil2d_gt.cc:615,624).  n <= stage_cap.

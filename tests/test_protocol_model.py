@@ -47,6 +47,15 @@ def test_ll_allreduce_single_cell_set_loses_values():
         check(ll_allreduce_model, n_ranks=2, calls=2, buffers=1)
 
 
+def test_gather_between_reductions_must_not_let_senders_run_ahead():
+    """Why gmt_gather_f64 ends with an all-to-all round although only the root needs the data: the
+    reductions' cells are double-buffered by epoch parity, which holds only if no collective lets a
+    rank get more than one call ahead of another."""
+    with pytest.raises(ProtocolViolation, match="deadlock"):
+        check(ll_allreduce_model, n_ranks=3, calls=3, buffers=2, gather_between="nowait")
+    assert check(ll_allreduce_model, n_ranks=3, calls=3, buffers=2, gather_between="barrier") > 50
+
+
 def test_checker_reports_deadlock():
     from gpu_mpi_tests_b200.utils.protocol_model import explore
     never = ("wait", lambda mem, p: False)
