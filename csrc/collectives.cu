@@ -548,7 +548,7 @@ int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, in
   int grid = 0;
   // LL needs no grid-wide rendezvous, so it can afford one element per thread; the others keep few CTAs
   const int64_t per_cta = algo == 3 ? kCollThreads : kCollThreads * 4;
-  int rc = coll_grid(k, std::min<int64_t>((n + per_cta - 1) / per_cta, 64), n_ranks, &grid);
+  int rc = coll_grid(k, (n + per_cta - 1) / per_cta, n_ranks, &grid);
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&n};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));

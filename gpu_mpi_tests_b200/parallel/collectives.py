@@ -130,16 +130,17 @@ class PeerCollectives:
             raise ValueError(f"buffer of {self.buf_doubles} doubles cannot hold {self.world} slices of {n}")
 
     ALGOS = {"one_shot": 0, "two_shot": 1, "multimem": 2, "ll": 3}
-    LL_MAX = 32768   # doubles: beyond this the 16-byte-per-double-per-peer cells stop paying
+    LL_MAX = 1 << 18   # doubles x ranks: beyond this the 16-byte-per-double-per-peer cells stop paying
+    #                    (2 MiB on 2 GPUs: 15.7 us LL vs 30 us one-shot; on 4 GPUs: 34 vs 33 us)
 
     def allreduce(self, vec: dict, out: dict | None = None, algo: str = "auto") -> None:
         """out[r] <- sum over ranks of vec[r]; in place when out is None.  algo: "ll" (epoch-carrying
-        16-byte cells, no rendezvous), "one_shot", "two_shot", "multimem"; "auto" = ll up to LL_MAX
-        doubles, two_shot beyond 2^17 doubles on 8+ ranks, else one_shot."""
+        16-byte cells, no rendezvous), "one_shot", "two_shot", "multimem"; "auto" = ll while
+        n * world <= LL_MAX, two_shot beyond 2^17 doubles on 8+ ranks, else one_shot."""
         out = out or vec
         n = next(iter(vec.values())).numel()
         if algo == "auto":
-            algo = "ll" if n <= self.LL_MAX else ("two_shot" if (n > (1 << 17) and self.world >= 8) else "one_shot")
+            algo = "ll" if n * self.world <= self.LL_MAX else ("two_shot" if (n > (1 << 17) and self.world >= 8) else "one_shot")
         if n > self.stage_cap:
             raise ValueError(f"all-reduce of {n} doubles exceeds the staging capacity {self.stage_cap}")
         if algo == "multimem" and not self.has_multicast:
