@@ -309,3 +309,30 @@ def test_native_mpienv_program():
     res = subprocess.run([str(exe), "--ranks", "3"], capture_output=True, text=True, env=dict(os.environ, MEMORY_PER_CORE="12"))
     assert res.returncode == 0
     assert res.stdout.splitlines() == [report.mpienv_line(r, 12) for r in range(3)]
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` must print one JSON line {"impl": "reference", "unavailable": ...}
+    and exit 0 (the reference is a flat tree of MPI programs that cannot be installed here)."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    res = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "2",
+                          "--warmup", "3"], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    lines = [ln for ln in res.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    rec = json.loads(lines[0])
+    assert rec["impl"] == "reference" and isinstance(rec["unavailable"], str) and "\n" not in rec["unavailable"]
+
+
+def test_bench_json_keys_are_the_contract():
+    """Static check of the keys bench.py emits (the GPU run itself is the driver's job)."""
+    from pathlib import Path
+    src = (Path(__file__).resolve().parents[1] / "bench.py").read_text()
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "h2d_bytes_per_step", "d2h_bytes_per_step",
+                "gpu_launches", "sm_mhz", "sm_max_mhz", "reasons"):
+        assert f'"{key}"' in src, key
