@@ -18,7 +18,6 @@ fused path runs axis-sum + all-reduce as one kernel (device-timed), the baseline
 library all_reduce alone with the host clock, as the reference does."""
 from __future__ import annotations
 
-import math
 import sys
 import time
 

@@ -13,7 +13,6 @@ from __future__ import annotations
 import torch
 
 from ..utils import oracle
-from . import _lib
 from ._lib import lib
 
 F64 = torch.float64

@@ -11,8 +11,6 @@ host synchronisation.  Under `VirtualSpace` all ranks run in one cooperative lau
 """
 from __future__ import annotations
 
-import ctypes as C
-
 import torch
 
 from ..ops._lib import CollRank, lib

@@ -14,11 +14,9 @@ ranks on one GPU and `step()` runs them in one cooperative launch.
 """
 from __future__ import annotations
 
-import ctypes as C
-
 import torch
 
-from ..ops import _lib, local
+from ..ops import local
 from ..ops._lib import Halo1dRank, Halo2dRank, lib
 from .decomp import Grid2D, Slab1D
 from .symm import PeerSpace, SymmHeap
