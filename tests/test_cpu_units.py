@@ -336,3 +336,20 @@ def test_bench_json_keys_are_the_contract():
                 "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "h2d_bytes_per_step", "d2h_bytes_per_step",
                 "gpu_launches", "sm_mhz", "sm_max_mhz", "reasons"):
         assert f'"{key}"' in src, key
+
+
+def test_public_header_is_plain_c(tmp_path):
+    """include/gmt_b200.h is the C ABI: it must compile as C99 with no CUDA header around."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("gcc not found")
+    src = tmp_path / "abi.c"
+    src.write_text('#include "gmt_b200.h"\nint main(void) { gmt_halo2d_rank r; gmt_coll_rank c; (void)r; (void)c; '
+                   'return gmt_version() > 0 ? 0 : 1; }\n')
+    inc = str(Path(__file__).resolve().parents[1] / "include")
+    res = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", str(src)],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
