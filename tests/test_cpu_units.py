@@ -353,3 +353,42 @@ def test_public_header_is_plain_c(tmp_path):
     res = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", str(src)],
                          capture_output=True, text=True)
     assert res.returncode == 0, res.stderr
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """The Python layer fills gmt_halo1d_rank / gmt_halo2d_rank / gmt_coll_rank / gmt_device_props through
+    ctypes mirrors; a field added on one side only would corrupt memory silently.  Compile a C program
+    that prints sizeof and every offsetof, and compare with the ctypes layout."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    from gpu_mpi_tests_b200.ops import _lib
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("gcc not found")
+    pairs = {"gmt_halo1d_rank": _lib.Halo1dRank, "gmt_halo2d_rank": _lib.Halo2dRank, "gmt_coll_rank": _lib.CollRank,
+             "gmt_device_props": _lib.DeviceProps}
+    rename = {"inp": "in"}   # `in` is a keyword-ish name on the Python side
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "gmt_b200.h"', 'int main(void) {']
+    for cname, cls in pairs.items():
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _t in cls._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {rename.get(fname, fname)}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines) + "\n")
+    exe = tmp_path / "layout"
+    inc = str(Path(__file__).resolve().parents[1] / "include")
+    res = subprocess.run([gcc, "-std=c99", "-I", inc, str(src), "-o", str(exe)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    out = subprocess.run([str(exe)], capture_output=True, text=True).stdout.split("\n")
+    got = {tuple(ln.split()[:2]): int(ln.split()[2]) for ln in out if ln.strip()}
+    for cname, cls in pairs.items():
+        assert got[(cname, "size")] == C_sizeof(cls), cname
+        for fname, _t in cls._fields_:
+            assert got[(cname, fname)] == getattr(cls, fname).offset, (cname, fname)
+
+
+def C_sizeof(cls) -> int:
+    import ctypes
+    return ctypes.sizeof(cls)
