@@ -392,3 +392,29 @@ def test_ctypes_structs_match_the_c_header(tmp_path):
 def C_sizeof(cls) -> int:
     import ctypes
     return ctypes.sizeof(cls)
+
+
+def test_header_library_and_binding_agree_on_entry_points():
+    """Every function the header declares is exported by the built library, and every name the
+    ctypes table binds is declared in the header (argument counts included)."""
+    import re
+    import subprocess
+    from pathlib import Path
+    from gpu_mpi_tests_b200.ops import _lib
+    if not _lib.have_native():
+        pytest.skip("library not built")
+    root = Path(__file__).resolve().parents[1]
+    text = (root / "include" / "gmt_b200.h").read_text()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    decls = {}
+    for m in re.finditer(r"\b(gmt_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
+        args = m.group(2).strip()
+        decls[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    assert len(decls) > 70
+    exported = subprocess.run(["nm", "-D", "--defined-only", str(_lib.LIB_PATH)], capture_output=True, text=True).stdout
+    exported = {ln.split()[-1] for ln in exported.splitlines() if ln.strip()}
+    missing = sorted(set(decls) - exported)
+    assert not missing, f"declared but not exported: {missing}"
+    for name, (_res, argtypes) in _lib._SIGS.items():
+        assert name in decls, f"{name} is bound in _lib.py but not declared in the header"
+        assert len(argtypes) == decls[name], f"{name}: {len(argtypes)} ctypes arguments, {decls[name]} in the header"
