@@ -24,6 +24,7 @@
 
 #include "p2p.cuh"
 #include "stencil_tiles.cuh"
+#include "tile_order.h"
 #include "tma.cuh"
 
 namespace gmt {
@@ -234,40 +235,7 @@ __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e,
 }
 
 // ====================================================================== 2-D
-struct TileMap {
-  int64_t tiles_i, tiles_j, a0, a1, b0, b1, ni, nj, n_int;
-};
-
-// counter value -> tile, interior tiles first, boundary tiles after them
-__device__ __forceinline__ void decode_tile(const TileMap& M, int64_t c, int64_t& ti, int64_t& tj)
-{
-  if (c < M.n_int) {
-    tj = M.b0 + c / M.ni;
-    ti = M.a0 + c % M.ni;
-    return;
-  }
-  int64_t k = c - M.n_int;
-  if (M.n_int == 0) {
-    tj = k / M.tiles_i;
-    ti = k % M.tiles_i;
-    return;
-  }
-  const int64_t nbot = M.b0 * M.tiles_i, ntop = (M.tiles_j - M.b1) * M.tiles_i;
-  if (k < nbot) {
-    tj = k / M.tiles_i;
-    ti = k % M.tiles_i;
-  } else if (k < nbot + ntop) {
-    k -= nbot;
-    tj = M.b1 + k / M.tiles_i;
-    ti = k % M.tiles_i;
-  } else {
-    k -= nbot + ntop;
-    const int64_t nside = M.tiles_i - M.ni;
-    tj = M.b0 + k / nside;
-    const int64_t idx = k % nside;
-    ti = idx < M.a0 ? idx : M.a1 + (idx - M.a0);
-  }
-}
+// (TileMap / decode_tile: tile_order.h)
 
 // kOneShot = false: persistent grid, tiles drawn from a counter -- needed when several virtual
 //   ranks share one cooperative launch (every CTA must be resident for the spin-waits to be safe).
@@ -292,20 +260,12 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
   const int par = (int)(e & 1);
   const int tid = threadIdx.x;
   const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
-  TileMap M;
-  M.tiles_i = (nx + kTileI - 1) / kTileI;
-  M.tiles_j = (ny + TJ - 1) / TJ;
   // x-face tiles (first / last row-tile of every column block) stay where memory order puts them:
   // pulling them out leaves 8 KB holes in every column for a later pass and costs more bandwidth
   // than the few waits at the very start of the kernel (measured 0.6725 vs 0.6796 ms at 2 GPUs).
   // y-face tiles are whole column blocks (contiguous), so they are deferred to the end for free.
-  M.a0 = (!natural && GX && R.has[0]) ? 1 : 0;
-  M.a1 = max(M.a0, M.tiles_i - ((!natural && GX && R.has[1]) ? 1 : 0));
-  M.b0 = (GY && R.has[2]) ? 1 : 0;
-  M.b1 = max(M.b0, M.tiles_j - ((GY && R.has[3]) ? 1 : 0));
-  M.ni = M.a1 - M.a0;
-  M.nj = M.b1 - M.b0;
-  M.n_int = M.ni * M.nj;
+  const TileMap M = tile_map_make((nx + kTileI - 1) / kTileI, (ny + TJ - 1) / TJ, GX && R.has[0], GX && R.has[1],
+                                  GY && R.has[2], GY && R.has[3], natural);
   const int64_t ntiles = M.tiles_i * M.tiles_j;
 
   push_faces<GX, GY, kDebug>(R, e, par, M.tiles_i);

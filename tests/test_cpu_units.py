@@ -418,3 +418,23 @@ def test_header_library_and_binding_agree_on_entry_points():
     for name, (_res, argtypes) in _lib._SIGS.items():
         assert name in decls, f"{name} is bound in _lib.py but not declared in the header"
         assert len(argtypes) == decls[name], f"{name}: {len(argtypes)} ctypes arguments, {decls[name]} in the header"
+
+
+def test_tile_order_is_a_bijection(tmp_path):
+    """csrc/tile_order.h on the host: the fused 2-D kernel's counter -> tile map visits every tile
+    exactly once for every grid shape / neighbour combination / order flag, never schedules a tile
+    that needs no flag after one that does, and degenerates to memory order when nothing is deferred."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    gxx = shutil.which("g++")
+    if not gxx:
+        pytest.skip("g++ not found")
+    root = Path(__file__).resolve().parents[1]
+    exe = tmp_path / "tile_order"
+    res = subprocess.run([gxx, "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I", str(root / "csrc"),
+                          str(root / "tests" / "native" / "test_tile_order.cpp"), "-o", str(exe)],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert run.returncode == 0 and run.stdout.startswith("ok "), run.stdout
