@@ -438,3 +438,21 @@ def test_tile_order_is_a_bijection(tmp_path):
     assert res.returncode == 0, res.stderr
     run = subprocess.run([str(exe)], capture_output=True, text=True)
     assert run.returncode == 0 and run.stdout.startswith("ok "), run.stdout
+
+
+def test_pure_host_entry_points_work_without_a_gpu():
+    """Entry points that only compute sizes must work on a machine with no GPU (plan set-up code
+    calls them before touching a device)."""
+    from gpu_mpi_tests_b200.ops import _lib
+    if not _lib.have_native():
+        pytest.skip("library not built")
+    lib = _lib.lib
+    assert lib.gmt_version() >= 100
+    for nx, ny in [(1024, 524288), (16384, 16384), (8, 4), (4100, 1025)]:
+        assert lib.gmt_halo2d_flag_count(0, nx, ny) == lib.gmt_halo2d_flag_count(1, nx, ny) == -(-ny // 1024)
+        assert lib.gmt_halo2d_flag_count(2, nx, ny) == lib.gmt_halo2d_flag_count(3, nx, ny) == -(-nx // 1024)
+    assert lib.gmt_reduce_scratch_bytes() >= 4096
+    assert lib.gmt_noalloc_max_n() == 33_554_432 and lib.gmt_noalloc_scratch_bytes() == 65_792
+    n = __import__("ctypes").c_int(-1)
+    lib.gmt_device_count(__import__("ctypes").byref(n))    # no driver / no device -> 0, not an error
+    assert n.value >= 0
