@@ -3,13 +3,10 @@
 CUDA-event timings of every single-GPU kernel at the BASELINE shapes.  Writes
 gpurun_out/probe.json.  (Development tool; the product benchmarks live in bench.py and
 benchmarks/.)"""
-import ctypes as C
 import json
-import os
 import shutil
 import subprocess
 import sys
-import time
 from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))

@@ -6,7 +6,6 @@ import csv
 import io
 import json
 import subprocess
-import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parents[1]

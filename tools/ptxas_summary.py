@@ -3,7 +3,6 @@
 import glob
 import re
 import subprocess
-import sys
 from pathlib import Path
 
 obj = Path(__file__).resolve().parents[1] / "gpu_mpi_tests_b200" / "_native" / "obj"

@@ -4,7 +4,6 @@
 multimem), from `cuobjdump -sass` of the built library.  Writes profiles/sass_evidence.md."""
 import re
 import subprocess
-import sys
 from collections import OrderedDict
 from pathlib import Path
 
