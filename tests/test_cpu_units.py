@@ -489,3 +489,24 @@ def test_coverage_map_points_at_real_files_and_tests():
             assert (root / real).exists(), f"{path} named in COVERAGE.md does not exist"
             checked += 1
     assert checked > 150
+
+
+def test_reported_numbers_match_the_committed_records():
+    """README.md / BASELINE.md quote the flagship numbers of profiles/bench_n{1,2,4,8}.json: the quoted
+    GLUP/s must be the recorded ones (rounded), and the records must satisfy the bench contract."""
+    import json
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    readme, baseline = (root / "README.md").read_text(), (root / "BASELINE.md").read_text()
+    for n in (1, 2, 4, 8):
+        rec = json.loads((root / "profiles" / f"bench_n{n}.json").read_text().strip().splitlines()[-1])
+        assert rec["metric"] == "stencil2d_glups" and rec["n_gpus"] == n and rec["warmup"] >= 3 and rec["dtype"] == "fp64"
+        assert rec["e2e"]["h2d_bytes_per_step"] > 0 and rec["e2e"]["d2h_bytes_per_step"] > 0
+        assert rec["e2e"]["value"] < rec["value"]                      # end to end cannot beat the device time
+        assert rec["gpu_launches"] == rec["steps"]                     # one fused kernel per step
+        assert not set(rec["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+        assert 0.9 < rec["roofline"]["frac_of_measured_copy_peak"] < 1.1
+        quoted = f"{rec['value']:.0f}"
+        assert quoted in baseline, f"{quoted} GLUP/s (N={n}) is not in BASELINE.md"
+        if n in (1, 8):
+            assert quoted in readme, f"{quoted} GLUP/s (N={n}) is not in README.md"
