@@ -13,12 +13,30 @@ whole 16384^2 tile, plus the in-kernel error norm against the analytic derivativ
 device with CUDA events, max over ranks.  The input (2 GiB) and output (2 GiB) per GPU exceed
 the 126 MB L2, so no L2 flush is needed between iterations.
 
-`e2e` runs the same step through the public API `Stencil2DWorkload.step_e2e()`: every step
-uploads the physical-boundary ghost values from pinned host memory, runs the fused kernel and
-reads the error norm back to the host.
+`e2e` runs the same step through the public API `Stencil2DWorkload.step_e2e_pipelined()`: every
+step uploads that step's physical-boundary ghost values from pinned host memory, runs the fused
+kernel and copies the error norm to pinned host memory, where the host reads it one call later
+(`e2e.sync_value`: the synchronous `step_e2e()`, which reads it before the next step starts).
 
-Extra keys (`extra`) report the other BASELINE configs at the same N: 1-D stencil GLUP/s,
-daxpy+global-sum GB/s, exposed halo-exchange microseconds.
+Same-box anchor: the reference arm cannot run here (see `--impl reference`), so the default run
+ALSO times the library-only restatement of the reference's algorithm (`gpu_mpi_tests_b200.baseline`:
+pack kernels, NCCL send/recv, unpack kernels, device-wide syncs, un-fused stencil -- the same code
+`--impl baseline` runs alone) in the same process on the same GPUs: `vs_baseline` = value / that
+arm's value, details in `baseline_arm`.
+
+`extra` carries the rest of BASELINE.json's metric at this N, every row for both arms ("fused" =
+peer-memory kernels, "lib" = NCCL / torch library calls), device-timed, max over ranks:
+  halo_exchange_us      the exchange alone (the reference's timed quantity): flagship faces
+                        (4 x 128 KiB), 8 MiB strided (dim-0 slab), 8 MiB contiguous (dim-1 slab), 16 B (1-D)
+  daxpy_sum             daxpy + global sum, n = 2^20 per rank and n = 48 Mi / N: us and GB/s per GPU
+  allreduce_8KiB_us     in-place all-reduce of 1024 doubles (test_sum)
+  allgather             in-place allgather, 64 KiB and 256 MiB slices: us and ingress GB/s per GPU
+  barrier_us
+  stencil1d / stencil2d_ref_dim0 / _dim1 / stencil2d_periodic4   GLUP/s of the other stencil configs
+                        (periodic4: wrapped process grid, every rank has four live faces)
+  ghost_mismatch        after the timed loop the field is changed, one more fused step runs, and
+                        every ghost cell is compared with the neighbour's boundary value (NCCL
+                        all_gather of the boundary strips, outside any timed region): count over all ranks
 
 `--impl reference` reports why the unmodified reference cannot run here.
 """
@@ -47,7 +65,70 @@ def parse():
     ap.add_argument("--impl", default="fused", choices=["fused", "baseline", "reference"])
     ap.add_argument("--n", type=int, default=16384, help="per-GPU tile edge (BASELINE config: 16384)")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary configs")
+    ap.add_argument("--no-baseline-arm", action="store_true", help="skip the library-only arm (vs_baseline stays null)")
     return ap.parse_args()
+
+
+def flagship(rt, args, impl: str, warmup: int, sampler=None) -> dict:
+    """Device-timed and end-to-end numbers of the 16384^2-per-GPU grid config for one arm."""
+    import torch
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.utils import timing
+    n = args.n
+    wl = Stencil2DWorkload(rt, n, n, mode="grid", impl=impl, with_err=True)
+    wl.setup()
+    wl.step()
+    torch.cuda.synchronize()
+    wl.check()
+    err0 = max(wl.err_norm(r) for r in wl.ranks)
+    t = timing.time_steps(wl.step, args.steps, warmup, rt.device)
+    wl.check()
+    points = n * n * rt.world_size
+    out = {"value": points / (t["ms_per_step"] * 1e-3) / 1e9, "ms_per_step": t["ms_per_step"],
+           "launches_per_step": wl.launches_per_step, "grid": [wl.px, wl.py],
+           "peer_memory": getattr(getattr(wl, "space", None), "kind", "n/a")}
+
+    # ---- end to end through the public API: H2D boundary values + step + D2H error norm
+    # (fused arm, host_fed plan: the boundary upload goes straight into the kernel's inbox on a side
+    # stream and overlaps the interior sweep -- the host is treated as one more neighbour)
+    wl_e = Stencil2DWorkload(rt, n, n, mode="grid", impl=impl, with_err=True, host_fed=(impl == "fused"))
+    wl_e.setup()
+    h2d, d2h = wl_e.e2e_bytes()
+    ts = timing.time_steps(wl_e.step_e2e, args.steps, warmup, rt.device)
+    out["e2e_sync"] = {"value": points / (ts["ms_per_step"] * 1e-3) / 1e9, "ms_per_step": ts["ms_per_step"]}
+    if impl == "fused":
+        # pipelined: step s+1 is enqueued before step s's result is read; the flush (read of the last
+        # result) is inside the timed region
+        te = timing.time_steps(wl_e.step_e2e_pipelined, args.steps, warmup, rt.device, tail=wl_e.e2e_flush)
+    else:
+        te = ts
+    wl_e.check()
+    err_e = max(wl_e.err_norm(r) for r in wl_e.ranks)
+    del wl_e
+    torch.cuda.empty_cache()
+    out["e2e"] = {"value": points / (te["ms_per_step"] * 1e-3) / 1e9, "unit": "GLUP/s", "ms_per_step": te["ms_per_step"],
+                  "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                  "how": ("step_e2e_pipelined(): result read one call later" if impl == "fused" else "step_e2e()"),
+                  "sync_value": out["e2e_sync"]["value"], "sync_ms_per_step": out["e2e_sync"]["ms_per_step"]}
+    if sampler is not None:
+        # a 20-step region lasts ~15 ms, shorter than nvidia-smi's sampling period: keep the same
+        # kernel running (untimed) until the sampler has seen the GPU under load a few times
+        # (the count is derived from the rank-reduced step time, so every rank runs the same number
+        # of steps -- the fused kernels of neighbouring ranks must stay in lock-step)
+        for _ in range(min(2000, int(500.0 / max(t["ms_per_step"], 1e-3)))):
+            wl.step()
+        torch.cuda.synchronize()
+        out["clocks"] = sampler.stop()
+    err1 = rt.reduce_scalar(max(wl.err_norm(r) for r in wl.ranks), "max")
+    out["err_norm_max"] = max(err0, err1, err_e)
+    if impl == "fused":
+        try:
+            out["ghost_mismatch"] = wl.verify_ghosts()
+        except Exception as e:  # noqa: BLE001
+            out["ghost_mismatch"] = repr(e)
+    del wl
+    torch.cuda.empty_cache()
+    return out
 
 
 def main() -> int:
@@ -57,10 +138,8 @@ def main() -> int:
             print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
         return 0
 
-    import torch
     from gpu_mpi_tests_b200._native.build import ensure_built
-    ensure_built()   # a fresh checkout has no build outputs; no-op when the library is there
-    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    ensure_built()   # a fresh checkout has no build outputs; no-op when the library is up to date
     from gpu_mpi_tests_b200.parallel import runtime
     from gpu_mpi_tests_b200.utils import timing
 
@@ -71,43 +150,22 @@ def main() -> int:
     if rt.world_size != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={rt.world_size}: launch with torchrun --nproc-per-node {args.gpus}")
     n = args.n
-    wl = Stencil2DWorkload(rt, n, n, mode="grid", impl=args.impl, with_err=True)
-    wl.setup()
-    wl.step()
-    torch.cuda.synchronize()
-    wl.check()
-    err0 = max(wl.err_norm(r) for r in wl.ranks)
+    points = n * n * rt.world_size
 
-    # ---- device-timed region: K fused steps.  The clock sampler runs from before the warm-up to
-    # after the end-to-end loop, i.e. only while the GPU is under this benchmark's load.
+    # the clock sampler runs from before the warm-up of the judged arm to after its end-to-end loop,
+    # i.e. only while the GPU is under this benchmark's load
     sampler = timing.ClockSampler(rt.device.index, period_ms=50)
     sampler.start()
-    t = timing.time_steps(wl.step, args.steps, warmup, rt.device)
-    wl.check()
-    points = n * n * rt.world_size
-    glups = points / (t["ms_per_step"] * 1e-3) / 1e9
+    main_arm = flagship(rt, args, args.impl, warmup, sampler)
+    clocks = main_arm.pop("clocks", {})
 
-    # ---- end to end through the public API: H2D boundary values + step + D2H error norm
-    # (host_fed plan: the boundary upload goes straight into the kernel's inbox on a side stream and
-    # overlaps the interior sweep -- the host is treated as one more neighbour)
-    wl_e = Stencil2DWorkload(rt, n, n, mode="grid", impl=args.impl, with_err=True, host_fed=(args.impl == "fused"))
-    wl_e.setup()
-    h2d, d2h = wl_e.e2e_bytes()
-    te = timing.time_steps(wl_e.step_e2e, args.steps, warmup, rt.device)
-    wl_e.check()
-    err_e = max(wl_e.err_norm(r) for r in wl_e.ranks)
-    del wl_e
-    torch.cuda.empty_cache()
-    e2e_glups = points / (te["ms_per_step"] * 1e-3) / 1e9
-    # a 20-step region lasts ~15 ms, shorter than nvidia-smi's sampling period: keep the same
-    # kernel running (untimed) until the sampler has seen the GPU under load a few times
-    # (the count is derived from the rank-reduced step time, so every rank runs the same number
-    # of steps -- the fused kernels of neighbouring ranks must stay in lock-step)
-    for _ in range(min(2000, int(500.0 / max(t["ms_per_step"], 1e-3)))):
-        wl.step()
-    torch.cuda.synchronize()
-    clocks = sampler.stop()
-    err1 = rt.reduce_scalar(max(wl.err_norm(r) for r in wl.ranks), "max")
+    base_arm, vs_baseline = None, None
+    if args.impl == "fused" and not args.no_baseline_arm:
+        try:
+            base_arm = flagship(rt, args, "baseline", warmup)
+            vs_baseline = main_arm["value"] / base_arm["value"]
+        except Exception as e:  # noqa: BLE001 - the anchor must not sink the headline
+            base_arm = {"error": repr(e)}
 
     peaks = {}
     try:
@@ -115,7 +173,7 @@ def main() -> int:
     except Exception:  # noqa: BLE001
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
-    per_gpu_gbs = 16.0 * n * n / (t["ms_per_step"] * 1e-3) / 1e9
+    per_gpu_gbs = 16.0 * n * n / (main_arm["ms_per_step"] * 1e-3) / 1e9
 
     extra = {}
     if not args.no_extra:
@@ -123,15 +181,15 @@ def main() -> int:
 
     rec = {
         "metric": "stencil2d_glups",
-        "value": glups,
+        "value": main_arm["value"],
         "unit": "GLUP/s",
         "n_gpus": rt.world_size,
         "steps": args.steps,
         "warmup": warmup,
-        "ms_per_step": t["ms_per_step"],
+        "ms_per_step": main_arm["ms_per_step"],
         "higher_is_better": True,
         "scaling": "weak",
-        "vs_baseline": None,
+        "vs_baseline": vs_baseline,
         "dtype": "fp64",
         "data": "synthetic (analytic field z = x^3 + y^2, device-initialised)",
         "impl": args.impl,
@@ -139,19 +197,27 @@ def main() -> int:
             "model": "2D fp64 5-point stencil d/dx+d/dy with 4-neighbour ghost exchange",
             "per_gpu_tile": [n, n],
             "global_points": points,
-            "parallelism": f"grid{wl.px}x{wl.py}",
+            "parallelism": "grid%dx%d" % tuple(main_arm["grid"]),
             "l2": "inputs larger than L2 (2 GiB in + 2 GiB out per GPU), no flush",
-            "peer_memory": getattr(getattr(wl, "space", None), "kind", "n/a"),
+            "peer_memory": main_arm["peer_memory"],
         },
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
                    "reasons": clocks.get("reasons", []), "samples": clocks.get("samples", 0),
                    "power_w_max": clocks.get("power_w_max")},
-        "e2e": {"value": e2e_glups, "unit": "GLUP/s", "ms_per_step": te["ms_per_step"],
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": args.steps * wl.launches_per_step,
+        "e2e": main_arm["e2e"],
+        "gpu_launches": args.steps * main_arm["launches_per_step"],
         "roofline": {"hbm_gbs_per_gpu": per_gpu_gbs, "frac_of_measured_copy_peak": per_gpu_gbs / hbm,
                      "measured_copy_peak_gbs": hbm},
-        "err_norm_max": max(err0, err1, err_e),
+        "err_norm_max": main_arm["err_norm_max"],
+        "ghost_mismatch": main_arm.get("ghost_mismatch"),
+        "vs_baseline_what": ("value / the library-only restatement of the reference's algorithm (pack kernels + NCCL "
+                             "send/recv + unpack kernels + syncs + un-fused stencil), same process, same GPUs, same steps; "
+                             "the reference publishes no numbers and cannot be built here"),
+        "baseline_arm": None if base_arm is None else (base_arm if "error" in base_arm else {
+            "value": base_arm["value"], "ms_per_step": base_arm["ms_per_step"], "e2e": base_arm["e2e"]["value"],
+            "e2e_ms_per_step": base_arm["e2e"]["ms_per_step"], "ratio": vs_baseline,
+            "e2e_ratio": main_arm["e2e"]["value"] / base_arm["e2e"]["value"],
+            "launches_per_step": base_arm["launches_per_step"], "err_norm_max": base_arm["err_norm_max"]}),
         "extra": extra,
     }
     if rt.rank == 0:
@@ -161,39 +227,162 @@ def main() -> int:
 
 
 def secondary(rt, args, warmup: int) -> dict:
-    """The other BASELINE configs at this N (short runs)."""
+    """The rest of BASELINE.json's metric at this N (short runs), both arms."""
     import torch
+    import torch.distributed as dist
+    from gpu_mpi_tests_b200.models.daxpy import DaxpyWorkload
+    from gpu_mpi_tests_b200.models.stencil1d import Stencil1DWorkload
     from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
-    from gpu_mpi_tests_b200.parallel.halo import FusedStencil1D
+    from gpu_mpi_tests_b200.parallel.collectives import PeerCollectives
+    from gpu_mpi_tests_b200.parallel.halo import FusedStencil2D
     from gpu_mpi_tests_b200.parallel.symm import make_space
     from gpu_mpi_tests_b200.utils import timing
     out = {}
     steps = max(5, min(args.steps, 20))
-    W = rt.world_size
-    try:
-        space = make_space(rt)
-        # 1-D stencil, 2^27 points per GPU (BASELINE config 2)
-        n1 = 1 << 27
-        p1 = FusedStencil1D(space, n1, with_err=False)
-        p1.init_analytic()
-        t = timing.time_steps(p1.step, steps, warmup, rt.device)
-        p1.check_status()
-        out["stencil1d_2p27_glups"] = n1 * W / (t["ms_per_step"] * 1e-3) / 1e9
-        out["stencil1d_ms_per_step"] = t["ms_per_step"]
-        del p1
+    W, dev, r = rt.world_size, rt.device, rt.rank
+    F64 = torch.float64
+
+    def guarded(name, fn):
+        try:
+            fn()
+        except Exception as e:  # noqa: BLE001 - secondary numbers must not sink the headline
+            out.setdefault("errors", {})[name] = repr(e)
+            torch.cuda.synchronize(dev)
         torch.cuda.empty_cache()
-        # reference-default 2-D slab tiles (1024 x 524288 per rank), dim 0 and dim 1
-        for mode, (nx, ny) in (("dim0", (1024, 524288)), ("dim1", (524288, 1024))):
-            wl = Stencil2DWorkload(rt, nx, ny, mode=mode, impl="fused", with_err=False, space=space)
+
+    def ms_of(fn, k=steps):
+        return timing.time_steps(fn, k, warmup, dev)["ms_per_step"]
+
+    def us_graph(fn, iters=50):
+        ms, how = timing.time_graph(fn, iters, 10, dev)
+        return ms * 1e3, how
+
+    space = make_space(rt)
+    out["peer_space"] = space.kind
+
+    # ---- stencils: GLUP/s of the other configs + the exchange alone, both arms
+    def stencil1d():
+        n1 = 1 << 27                                     # BASELINE config 2
+        rec = {}
+        for impl, tag in (("fused", "fused"), ("baseline", "lib")):
+            wl = Stencil1DWorkload(rt, n1, impl=impl, with_err=False, space=space if impl == "fused" else None)
             wl.setup()
-            t = timing.time_steps(wl.step, steps, warmup, rt.device)
+            ms = ms_of(wl.step)
+            ex = ms_of(wl.exchange_only, 50)
             wl.check()
-            out[f"stencil2d_ref_{mode}_glups"] = nx * ny * W / (t["ms_per_step"] * 1e-3) / 1e9
-            out[f"stencil2d_ref_{mode}_ms_per_step"] = t["ms_per_step"]
+            rec[tag] = {"glups": n1 * W / (ms * 1e-3) / 1e9, "ms_per_step": ms, "exchange_us": ex * 1e3}
             del wl
             torch.cuda.empty_cache()
-    except Exception as e:  # noqa: BLE001 - secondary numbers must not sink the headline
-        out["error"] = repr(e)
+        out["stencil1d_2p27"] = rec
+        out["stencil1d_2p27_glups"] = rec["fused"]["glups"]
+        out["stencil1d_ms_per_step"] = rec["fused"]["ms_per_step"]
+        out.setdefault("halo_exchange_us", {})["1d_16B"] = {k: v["exchange_us"] for k, v in rec.items()}
+
+    def slabs():
+        # reference-default 2-D slab tiles (1024 x 524288 per rank): dim 0 = strided 8 MiB faces, dim 1 = contiguous
+        for mode, (nx, ny), label in (("dim0", (1024, 524288), "dim0_8MiB_strided"),
+                                      ("dim1", (524288, 1024), "dim1_8MiB_contiguous")):
+            rec = {}
+            for impl, tag in (("fused", "fused"), ("baseline", "lib")):
+                wl = Stencil2DWorkload(rt, nx, ny, mode=mode, impl=impl, with_err=False,
+                                       space=space if impl == "fused" else None, stage="device")
+                wl.setup()
+                ms = ms_of(wl.step)
+                ex = ms_of(wl.exchange)
+                wl.check()
+                rec[tag] = {"glups": nx * ny * W / (ms * 1e-3) / 1e9, "ms_per_step": ms, "exchange_us": ex * 1e3}
+                del wl
+                torch.cuda.empty_cache()
+            out[f"stencil2d_ref_{mode}"] = rec
+            out[f"stencil2d_ref_{mode}_glups"] = rec["fused"]["glups"]
+            out[f"stencil2d_ref_{mode}_ms_per_step"] = rec["fused"]["ms_per_step"]
+            out.setdefault("halo_exchange_us", {})[label] = {k: v["exchange_us"] for k, v in rec.items()}
+
+    def flagship_exchange():
+        n = args.n
+        rec = {}
+        for impl, tag in (("fused", "fused"), ("baseline", "lib")):
+            wl = Stencil2DWorkload(rt, n, n, mode="grid", impl=impl, with_err=False,
+                                   space=space if impl == "fused" else None, stage="device")
+            wl.setup()
+            rec[tag] = ms_of(wl.exchange, 50) * 1e3
+            wl.check()
+            if impl == "fused":
+                out["halo_bytes_out_per_gpu"] = wl.plan.halo_bytes_out(r)
+            del wl
+            torch.cuda.empty_cache()
+        out.setdefault("halo_exchange_us", {})["grid_faces_128KiB"] = rec
+
+    def periodic4():
+        # wrapped process grid: every rank exchanges all four faces whatever the grid shape
+        from gpu_mpi_tests_b200.parallel import decomp
+        n = args.n
+        px, py = decomp.best_grid(W)
+        plan = FusedStencil2D(space, px, py, n, n, 2, 2, with_err=False, periodic=True)
+        plan.init_analytic(poison=1e30)
+        ms = ms_of(plan.step)
+        ex = ms_of(plan.exchange, 50)
+        plan.check_status()
+        out["stencil2d_periodic4"] = {"glups": n * n * W / (ms * 1e-3) / 1e9, "ms_per_step": ms, "exchange_us": ex * 1e3,
+                                      "live_faces_per_rank": 4, "halo_bytes_out_per_gpu": plan.halo_bytes_out(r)}
+        del plan
+
+    # ---- daxpy + global sum (BASELINE config 4), both arms
+    def daxpy():
+        rec = {}
+        for n_el, label in ((1 << 20, "n_2p20"), ((48 << 20) // W, "n_48Mi_over_N")):
+            row = {"n_per_gpu": n_el}
+            for impl, tag in (("fused", "fused"), ("baseline", "lib")):
+                wl = DaxpyWorkload(rt, n_el, impl=impl, space=space if impl == "fused" else None, gather=False)
+                wl.allocate()
+                wl.initialize()
+                wl.a = 1e-9   # keep y bounded over many repetitions
+                us, how = us_graph(wl.global_sum_step) if n_el <= (1 << 20) else (ms_of(wl.global_sum_step) * 1e3, "eager")
+                wl.check()
+                row[tag] = {"us": us, "gbs_per_gpu": 24.0 * n_el / us / 1e3, "timing": how}
+                del wl
+                torch.cuda.empty_cache()
+            rec[label] = row
+        out["daxpy_sum"] = rec
+
+    # ---- collectives (BASELINE config 5 and test_sum), both arms
+    def collectives():
+        pc = PeerCollectives(space)
+        v = torch.ones(1024, dtype=F64, device=dev) * 1e-12
+        fused, how = us_graph(lambda: pc.allreduce({r: v}))
+        lib = us_graph(lambda: dist.all_reduce(v))[0] if W > 1 else None
+        out["allreduce_8KiB_us"] = {"fused": fused, "lib": lib, "timing": how}
+        fused, how = us_graph(pc.barrier)
+        tb = torch.zeros(1, device=dev)
+        lib = us_graph(lambda: dist.all_reduce(tb))[0] if W > 1 else None
+        out["barrier_us"] = {"fused": fused, "lib_allreduce_4B": lib, "timing": how}
+        pc.check_status()
+        del pc
+        rec = {}
+        for sbytes, label in ((1 << 16, "64KiB"), (1 << 28, "256MiB")):
+            n_el = sbytes // 8
+            pg = PeerCollectives(space, buf_doubles=n_el * W)
+            ref = torch.empty(n_el * W, dtype=F64, device=dev)
+            if sbytes <= (1 << 20):
+                fused = us_graph(lambda: pg.allgather_inplace(n_el))[0]
+                lib = us_graph(lambda: dist.all_gather_into_tensor(ref, ref[r * n_el:(r + 1) * n_el]))[0] if W > 1 else None
+            else:
+                fused = ms_of(lambda: pg.allgather_inplace(n_el), 5) * 1e3
+                lib = ms_of(lambda: dist.all_gather_into_tensor(ref, ref[r * n_el:(r + 1) * n_el]), 5) * 1e3 if W > 1 else None
+            pg.check_status()
+            rec[label] = {"fused_us": fused, "lib_us": lib,
+                          "fused_ingress_gbs_per_gpu": (W - 1) * sbytes / fused / 1e3,
+                          "lib_ingress_gbs_per_gpu": None if not lib else (W - 1) * sbytes / lib / 1e3}
+            del pg, ref
+            torch.cuda.empty_cache()
+        out["allgather"] = rec
+
+    guarded("stencil1d", stencil1d)
+    guarded("slabs", slabs)
+    guarded("flagship_exchange", flagship_exchange)
+    guarded("periodic4", periodic4)
+    guarded("daxpy", daxpy)
+    guarded("collectives", collectives)
     return out
 
 

@@ -45,33 +45,8 @@ def t_ms(fn, steps, warmup, dev):
 
 
 def graph_ms(fn, iters, warmup, dev):
-    """Latency of a launch-bound op: `iters` calls captured in ONE CUDA graph and replayed, so the
-    Python/driver launch cost is out of the measurement for the fused and the NCCL path alike.
-    Falls back to eager event timing when the op cannot be captured."""
-    try:
-        for _ in range(warmup):
-            fn()
-        torch.cuda.synchronize(dev)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            for _ in range(iters):
-                fn()
-        g.replay()
-        torch.cuda.synchronize(dev)
-        if dist.is_initialized():
-            dist.barrier(device_ids=[dev.index])
-        torch.cuda.synchronize(dev)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        g.replay()
-        e1.record()
-        torch.cuda.synchronize(dev)
-        ms = e0.elapsed_time(e1) / iters
-        del g
-        return timing.max_over_ranks(ms, dev), "graph"
-    except Exception:  # noqa: BLE001
-        torch.cuda.synchronize(dev)
-        return t_ms(fn, iters, warmup, dev), "eager"
+    """Latency of a launch-bound op: see utils/timing.time_graph."""
+    return timing.time_graph(fn, iters, warmup, dev)
 
 
 def free():

@@ -24,7 +24,11 @@ namespace gmt {
 constexpr int kCollThreads = 512;
 constexpr int kRoundStride = 32;  // words per signalling round in a flag block
 constexpr int kLLBase = 64;       // LL slots: [parity][src rank][2 words] after the two rounds
-constexpr int64_t kLLMaxDoubles = 32768;  // vectors up to 256 KiB travel as LL cells by default
+constexpr int64_t kLLMaxCells = 1LL << 18;  // n x world up to here: vectors travel as LL cells by default
+//   (same rule as parallel/collectives.py: each double costs 16 bytes per peer, so at 8 ranks the
+//   switch to one-/two-shot comes at 32 Ki doubles, at 2 ranks at 128 Ki)
+constexpr int64_t kLLGatherMax = 8192;      // allgather slices up to 64 KiB can travel as LL cells
+constexpr uint32_t kStatusTooBig = 0x1000u; // status word: the call needed more LL cells than stage_cap
 
 struct CollShared {
   gmt_coll_rank R;
@@ -108,6 +112,18 @@ __device__ __forceinline__ void coll_finish(CollShared& S, uint64_t e)
   }
 }
 
+// weak (unqualified) multimem.st: ordering comes from the fence + flag that follow anyway
+__device__ __forceinline__ void multimem_st_32B_weak(double* mc, const double4_t& v)
+{
+  const float4* f = reinterpret_cast<const float4*>(&v);
+  asm volatile("multimem.st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(f[0].x), "f"(f[0].y), "f"(f[0].z),
+               "f"(f[0].w)
+               : "memory");
+  asm volatile("multimem.st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + 2), "f"(f[1].x), "f"(f[1].y), "f"(f[1].z),
+               "f"(f[1].w)
+               : "memory");
+}
+
 __device__ __forceinline__ void multimem_st_32B(double* mc, const double4_t& v)
 {
   // the bytes are what matters: 2 x multimem.st.v4.f32 carry 4 doubles to every GPU of the group
@@ -152,9 +168,16 @@ __global__ void __launch_bounds__(kCollThreads, 2)
         const double4_t a = ldg256(src + 4 * v);
         double4_t b;
         if (two) b = ldg256(src + 4 * (v + stride));
-        if (all && use_mc) {
+        if (all && use_mc == 1) {
           multimem_st_32B(S.R.mc_buf + off + 4 * v, a);
           if (two) multimem_st_32B(S.R.mc_buf + off + 4 * (v + stride), b);
+        } else if (all && use_mc == 3) {
+          multimem_st_32B_weak(S.R.mc_buf + off + 4 * v, a);
+          if (two) multimem_st_32B_weak(S.R.mc_buf + off + 4 * (v + stride), b);
+        } else if (all && use_mc == 4) {
+          // an ordinary store on the multicast mapping is replicated by the switch as well
+          stg256(S.R.mc_buf + off + 4 * v, a);
+          if (two) stg256(S.R.mc_buf + off + 4 * (v + stride), b);
         } else if (all) {
           // peers visited starting at r+1: at any moment the ranks target a permutation of
           // destinations instead of all hammering the same GPU's ingress port
@@ -196,6 +219,64 @@ __global__ void __launch_bounds__(kCollThreads, 2)
     wait_all(S, 1, e);
     coll_finish(S, e);
   }
+}
+
+// LL cells live behind the four staging vectors: word index 4*cap + ((parity*W + src)*cap + i)*2 of a
+// rank's staging area (see the LL all-reduce below).
+__device__ __forceinline__ uint64_t* ll_cell(const CollShared& S, int owner, int par, int src, int64_t i)
+{
+  return reinterpret_cast<uint64_t*>(S.stage[owner]) + 4 * S.R.stage_cap +
+         (((int64_t)par * S.R.world + src) * S.R.stage_cap + i) * 2;
+}
+
+// ---- small allgather through LL cells (slices up to 64 KiB).  The flag-based kernel above pays two
+// signalling rounds (entry: nobody's user buffer may be written before its owner is in the call;
+// exit: my slice has landed everywhere) = two NVLink round trips plus two fences.  Here nobody
+// writes anybody's USER buffer: every value goes into the peers' LL cell area (staging memory that
+// only collectives touch) as a 16-byte cell carrying the epoch in both words, and every rank copies
+// what arrives into its own buffer -- one one-way trip, no fence, no entry round.  The thread that
+// waits for a cell waits for another GPU only, so no co-residency is assumed.
+__global__ void __launch_bounds__(kCollThreads, 2)
+  gather_ll_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n, int from_in)
+{
+  __shared__ CollShared S;
+  const uint64_t e = coll_enter(S, ranks);
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
+  if (n > S.R.stage_cap) {   // CTA-uniform; every rank takes the same branch
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(S.R.status, kStatusTooBig);
+    if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
+    return;
+  }
+  double* own = S.buf[r];
+  const double* src = from_in ? S.R.in : own + (int64_t)r * n;
+  const int64_t stride = (int64_t)gridDim.x * kCollThreads;
+  const int64_t t0 = (int64_t)blockIdx.x * kCollThreads + threadIdx.x;
+  const uint64_t e32 = e & 0xffffffffull;
+  for (int64_t i = t0; i < n; i += stride) {
+    const double v = src[i];
+    for (int k = 1; k < W; ++k) st_ll_cell(ll_cell(S, (r + k) % W, par, r, i), v, e32);
+    if (from_in) own[(int64_t)r * n + i] = v;
+  }
+  const int64_t limit = S.R.spin_limit > 0 ? S.R.spin_limit : kDefaultSpinLimit;
+  const int64_t total = (int64_t)(W - 1) * n;
+  for (int64_t q = t0; q < total; q += stride) {
+    const int k = 1 + (int)(q / n);
+    const int64_t i = q - (int64_t)(k - 1) * n;
+    const int p = (r + k) % W;
+    const uint64_t* cell = ll_cell(S, r, par, p, i);
+    double v = 0.0;
+    bool ok = false;
+    for (int64_t it = 0; it < limit; ++it) {
+      if (ld_ll_cell(cell, e32, v)) {
+        ok = true;
+        break;
+      }
+      if (it > 64) __nanosleep(32);
+    }
+    if (!ok) atomicExch(S.R.status, 1u + p);
+    own[(int64_t)p * n + i] = v;
+  }
+  if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
 }
 
 // ============================================================ all-reduce building blocks
@@ -247,11 +328,6 @@ __device__ __forceinline__ void reduce_tail(CollShared& S, uint64_t e, int64_t n
 // staging vectors: word index 4*cap + ((parity*W + src)*cap + i)*2 of a rank's staging area.
 // Parity double-buffering is enough for the same reason as for the halo inboxes: a rank can only be
 // two calls ahead of a peer after that peer has read everything of the call in between.
-__device__ __forceinline__ uint64_t* ll_cell(const CollShared& S, int owner, int par, int src, int64_t i)
-{
-  return reinterpret_cast<uint64_t*>(S.stage[owner]) + 4 * S.R.stage_cap +
-         (((int64_t)par * S.R.world + src) * S.R.stage_cap + i) * 2;
-}
 __device__ __forceinline__ void ll_push(const CollShared& S, uint64_t e, int64_t i, double v)
 {
   const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
@@ -312,8 +388,37 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   reduce_tail<kAlgo>(S, e, n);
 }
 
-// axis sum straight into the staging area, then the all-reduce
-template <int kAlgo>
+// lanes 0..W-1 of a warp each fetch one rank's cell of index i; every lane returns the rank-ordered sum
+__device__ __forceinline__ double ll_collect_warp(CollShared& S, uint64_t e, int64_t i)
+{
+  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1), lane = threadIdx.x & 31;
+  const int64_t limit = S.R.spin_limit > 0 ? S.R.spin_limit : kDefaultSpinLimit;
+  double v = 0.0;
+  if (lane < W) {
+    const uint64_t* cell = ll_cell(S, r, par, lane, i);
+    bool ok = false;
+    for (int64_t it = 0; it < limit; ++it) {
+      if (ld_ll_cell(cell, e & 0xffffffffull, v)) {
+        ok = true;
+        break;
+      }
+      if (it > 64) __nanosleep(32);
+    }
+    if (!ok) atomicExch(S.R.status, 1u + lane);
+  }
+  double s = 0.0;
+  for (int src = 0; src < W; ++src) s += __shfl_sync(0xffffffffu, v, src);  // rank order: same bits everywhere
+  return s;
+}
+
+// axis sum straight into the staging area (or out as LL cells), then the all-reduce.  The LL /
+// one-shot choice is made in the kernel from the descriptor's world size, with the same rule as the
+// Python layer (n_out x world <= 2^18 cells and n_out <= stage_cap).
+// In the LL flavour the thread (warp) that pushed an index is the one that later collects it, so a
+// wait is only ever for ANOTHER rank's push, never for a sibling CTA of this grid: the kernel is safe
+// without a cooperative launch even when only part of the grid is resident (ranks sharing a GPU
+// across processes -- the MPS case the reference was written for, daxpy.cu:6-7 -- or another stream
+// holding SMs).
 __global__ void __launch_bounds__(kCollThreads, 2)
   axis_sum_allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t nx, int64_t ny, int64_t ld,
                             int axis, int64_t n_out)
@@ -321,13 +426,16 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   __shared__ CollShared S;
   __shared__ double tile[16][33];
   const uint64_t e = coll_enter(S, ranks);
+  const bool ll = n_out * S.R.world <= kLLMaxCells && n_out <= S.R.stage_cap;
   double* mine = S.stage[S.R.rank] + (int64_t)(e & 1) * S.R.stage_cap;
   const double* z = S.R.in;
+  double* out = S.R.out;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (axis == 0) {
     // out[j] = sum_i z(i,j): one warp per column, lanes along the contiguous axis
     const int64_t nwarps = (int64_t)gridDim.x * (kCollThreads / 32);
-    for (int64_t j = (int64_t)blockIdx.x * (kCollThreads / 32) + warp; j < n_out; j += nwarps) {
+    const int64_t jw = (int64_t)blockIdx.x * (kCollThreads / 32) + warp;
+    for (int64_t j = jw; j < n_out; j += nwarps) {
       const double* col = z + j * ld;
       double a0 = 0.0, a1 = 0.0;
       int64_t i = lane;
@@ -338,8 +446,14 @@ __global__ void __launch_bounds__(kCollThreads, 2)
       if (i < nx) a0 += col[i];
       const double s = warp_sum(a0 + a1);
       if (lane == 0) {
-        if (kAlgo == 3) ll_push(S, e, j, s);
+        if (ll) ll_push(S, e, j, s);
         else mine[j] = s;
+      }
+    }
+    if (ll) {
+      for (int64_t j = jw; j < n_out; j += nwarps) {   // the columns this warp pushed
+        const double s = ll_collect_warp(S, e, j);
+        if (lane == 0) out[j] = s;
       }
     }
   } else {
@@ -355,50 +469,63 @@ __global__ void __launch_bounds__(kCollThreads, 2)
         double s = 0.0;
 #pragma unroll
         for (int k = 0; k < kCollThreads / 32; ++k) s += tile[k][lane];
-        if (kAlgo == 3) ll_push(S, e, i, s);
+        if (ll) ll_push(S, e, i, s);
         else mine[i] = s;
       }
       __syncthreads();
     }
+    if (ll && warp == 0) {
+      for (int64_t i0 = (int64_t)blockIdx.x * 32; i0 < n_out; i0 += (int64_t)gridDim.x * 32) {
+        const int64_t i = i0 + lane;
+        if (i < n_out) out[i] = ll_collect(S, e, i);   // the rows this thread pushed
+      }
+    }
   }
-  if (kAlgo == 3) {
-    // the sums went out as LL cells the moment they were known; collecting needs no rendezvous
-    // (all CTAs of the grid are resident, so spinning on a cell a sibling CTA has yet to push is safe)
-    ll_tail(S, e, n_out);
+  if (ll) {
+    if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
     return;
   }
   publish_inputs(S, e);
-  reduce_tail<kAlgo == 3 ? 0 : kAlgo>(S, e, n_out);
+  reduce_tail<0>(S, e, n_out);
 }
 
 // ============================================================ daxpy + global sum
+// One-shot grid in address order (the pattern that gives the plain daxpy kernel 7 TB/s): CTA b
+// streams its contiguous share, reduces it, and stores the partial as an LL cell [parity][rank][b]
+// straight into EVERY rank's cell area -- no ticket, no fence, no last-CTA rendezvous.  The CTA with
+// the highest index then sums all world x grid cells as they turn up, in a fixed order, so every
+// rank gets the same bits and the result is reproducible run to run.  It waits only for cells, i.e.
+// for CTAs that themselves wait for nothing, so no co-residency is assumed.
+// (Round 1: persistent grid drawing 4096-element chunks from a counter with a barrier per chunk,
+// then ticket + partials re-read + one LL scalar per rank: 9.2 us at n = 2^20 on ONE GPU where the
+// stream itself takes 3.8 us.)
 constexpr int kDaUnroll = 2;
-constexpr int64_t kDaChunk = (int64_t)kCollThreads * kDaUnroll;
+constexpr int64_t kDaChunk = (int64_t)kCollThreads * kDaUnroll;   // 256-bit vectors per chunk
+constexpr int kDaMaxCtas = 2048;                                 // partial cells per rank (<= stage_cap)
 
 __global__ void __launch_bounds__(kCollThreads, 2)
-  daxpy_allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n, double a)
+  daxpy_allreduce_kernel(const gmt_coll_rank* __restrict__ ranks, int64_t n, double a, int chunks_per_cta)
 {
-  __shared__ CollShared S;
-  const uint64_t e = coll_enter(S, ranks);
-  const int W = S.R.world, r = S.R.rank, par = (int)(e & 1);
-  const double* __restrict__ x = S.R.in;
-  double* __restrict__ y = S.R.y;
+  __shared__ double red[40];
+  __shared__ double* stage_of[GMT_COLL_MAX_WORLD];
+  const gmt_coll_rank* Rg = ranks + blockIdx.y;
+  // operand pointers first (one broadcast load each), so the stream starts after ONE dependent load;
+  // everything the epilogue needs is fetched in the shadow of the stream
+  const double* __restrict__ x = Rg->in;
+  double* __restrict__ y = Rg->y;
+  const int tid = threadIdx.x;
+  const int64_t n4 = n / 4;
+  const bool vec = aligned(x, 32) && aligned(y, 32);
   double acc = 0.0;
-  if (aligned(x, 32) && aligned(y, 32)) {
-    const int64_t n4 = n / 4, nchunks = (n4 + kDaChunk - 1) / kDaChunk;
-    uint32_t* counter = S.R.done + 3;
-    // next chunk drawn while the current one streams (see daxpy.cu)
-    if (threadIdx.x == 0) S.next[0] = (int64_t)atomicAdd(counter, 1u);
-    __syncthreads();
-    int64_t c = S.next[0];
-    int slot = 0;
-    while (c < nchunks) {
-      unsigned int prefetched = 0;
-      if (threadIdx.x == 0) prefetched = atomicAdd(counter, 1u);
+  const int64_t c0 = (int64_t)blockIdx.x * chunks_per_cta;
+  if (vec) {
+    for (int q = 0; q < chunks_per_cta; ++q) {
+      const int64_t v0 = (c0 + q) * kDaChunk;
+      if (v0 >= n4) break;
       double4_t xv[kDaUnroll], yv[kDaUnroll];
 #pragma unroll
       for (int u = 0; u < kDaUnroll; ++u) {
-        const int64_t i = c * kDaChunk + threadIdx.x + (int64_t)u * kCollThreads;
+        const int64_t i = v0 + tid + (int64_t)u * kCollThreads;
         if (i < n4) {
           xv[u] = ldg256_stream(x + 4 * i);
           yv[u] = ldg256(y + 4 * i);
@@ -406,7 +533,7 @@ __global__ void __launch_bounds__(kCollThreads, 2)
       }
 #pragma unroll
       for (int u = 0; u < kDaUnroll; ++u) {
-        const int64_t i = c * kDaChunk + threadIdx.x + (int64_t)u * kCollThreads;
+        const int64_t i = v0 + tid + (int64_t)u * kCollThreads;
         if (i < n4) {
           yv[u].x = a * xv[u].x + yv[u].x;
           yv[u].y = a * xv[u].y + yv[u].y;
@@ -416,73 +543,92 @@ __global__ void __launch_bounds__(kCollThreads, 2)
           acc += (yv[u].x + yv[u].y) + (yv[u].z + yv[u].w);
         }
       }
-      if (threadIdx.x == 0) S.next[slot ^ 1] = (int64_t)prefetched;
-      __syncthreads();
-      slot ^= 1;
-      c = S.next[slot];
     }
-    if (blockIdx.x == 0) {
-      for (int64_t k = 4 * n4 + threadIdx.x; k < n; k += kCollThreads) {
+    if (blockIdx.x == gridDim.x - 1) {
+      for (int64_t k = 4 * n4 + tid; k < n; k += kCollThreads) {
         const double v = a * x[k] + y[k];
         y[k] = v;
         acc += v;
       }
     }
   } else {
-    for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kCollThreads) {
+    const int64_t lo = c0 * kDaChunk * 4, hi = min(n, (c0 + chunks_per_cta) * kDaChunk * 4);
+    const int64_t hi2 = blockIdx.x == gridDim.x - 1 ? n : hi;
+    for (int64_t i = lo + tid; i < hi2; i += kCollThreads) {
       const double v = a * x[i] + y[i];
       y[i] = v;
       acc += v;
     }
   }
-  const double part = block_sum(acc, S.red);
-  double total;
-  if (!grid_sum_last_block(part, S.R.scratch, S.red, total, gridDim.x, blockIdx.x)) return;
-  // Last CTA of this rank: one-shot all-reduce of the W rank totals in "LL" style -- every
-  // 8-byte word carries 32 bits of payload and the 32-bit epoch, so data and flag arrive
-  // together: no fence, no separate flag, no remote read; the cost is ONE one-way NVLink store
-  // latency.  (8-byte stores are single-copy atomic; slots are double-buffered by epoch parity.)
-  if (threadIdx.x == 0) S.red[0] = total;
-  __syncthreads();
+  // descriptor fields of the epilogue
+  const int W = Rg->world, r = Rg->rank;
+  const int64_t cap = Rg->stage_cap;
+  const uint64_t e = ld_relaxed_sys(Rg->epoch) + 1;
   const uint64_t e32 = e & 0xffffffffull;
-  bool ok = true;
-  if ((int)threadIdx.x < W) {
-    const uint64_t bits = (uint64_t)__double_as_longlong(S.red[0]);
-    uint64_t* dst = S.flag[threadIdx.x] + kLLBase + ((int64_t)par * GMT_COLL_MAX_WORLD + r) * 2;
-    st_relaxed_sys(dst, (bits & 0xffffffffull) | (e32 << 32));
-    st_relaxed_sys(dst + 1, (bits >> 32) | (e32 << 32));
-    const uint64_t* src = S.flag[r] + kLLBase + ((int64_t)par * GMT_COLL_MAX_WORLD + threadIdx.x) * 2;
-    const int64_t limit = S.R.spin_limit > 0 ? S.R.spin_limit : kDefaultSpinLimit;
-    uint64_t w0 = 0, w1 = 0;
-    ok = false;
+  const int par = (int)(e & 1);
+  if (tid < W) stage_of[tid] = Rg->peer_stage[tid];
+  const double part = block_sum(acc, red);   // (barriers inside: stage_of is visible afterwards)
+  if (tid == 0) red[32] = part;
+  __syncthreads();
+  const int G = (int)gridDim.x;
+  if ((int64_t)G > cap) {   // more partial cells than the staging area holds: report, do not scribble
+    if (blockIdx.x == G - 1 && tid == 0) {
+      atomicOr(Rg->status, kStatusTooBig);
+      *Rg->out = __longlong_as_double(0x7ff8000000000000LL);
+      st_relaxed_sys(Rg->epoch, e);
+    }
+    return;
+  }
+  auto cell_at = [&](int owner, int src, int64_t b) {
+    return reinterpret_cast<uint64_t*>(stage_of[owner]) + 4 * cap + (((int64_t)par * W + src) * cap + b) * 2;
+  };
+  if (tid < W) st_ll_cell(cell_at((r + tid) % W, r, blockIdx.x), red[32], e32);
+  if (blockIdx.x != G - 1) return;
+  // the collecting CTA: world x G cells in a fixed thread-strided order, then the block tree
+  const int64_t limit = Rg->spin_limit > 0 ? Rg->spin_limit : kDefaultSpinLimit;
+  double s = 0.0;
+  for (int64_t q = tid; q < (int64_t)W * G; q += kCollThreads) {
+    const int src = (int)(q / G);
+    const uint64_t* cell = cell_at(r, src, q - (int64_t)src * G);
+    double v = 0.0;
+    bool ok = false;
     for (int64_t it = 0; it < limit; ++it) {
-      w0 = ld_relaxed_sys(src);
-      w1 = ld_relaxed_sys(src + 1);
-      if ((w0 >> 32) == e32 && (w1 >> 32) == e32) {
+      if (ld_ll_cell(cell, e32, v)) {
         ok = true;
         break;
       }
       if (it > 64) __nanosleep(32);
     }
-    if (!ok) atomicExch(S.R.status, 1u + threadIdx.x);
-    S.red[1 + threadIdx.x] = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+    if (!ok) atomicExch(Rg->status, 1u + src);
+    s += v;
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int p = 0; p < W; ++p) s += S.red[1 + p];  // rank order: same bits on every rank
-    *S.R.out = s;
+  const double total = block_sum(s, red);
+  if (tid == 0) {
+    *Rg->out = total;
+    st_relaxed_sys(Rg->epoch, e);   // every CTA of this launch read the epoch before it pushed its cell
   }
-  coll_finish(S, e);
 }
 
-__global__ void __launch_bounds__(kCollThreads) barrier_kernel(const gmt_coll_rank* __restrict__ ranks)
+// One warp: flags and epoch are fetched side by side (two dependent loads instead of the generic
+// prologue's three), the release stores leave at once, and nothing is reset afterwards because the
+// barrier dirties no counter.
+__global__ void __launch_bounds__(32) barrier_kernel(const gmt_coll_rank* __restrict__ ranks)
 {
-  __shared__ CollShared S;
-  const uint64_t e = coll_enter(S, ranks);
-  signal_all(S, 0, e);
-  wait_all(S, 0, e);
-  coll_finish(S, e);
+  const gmt_coll_rank* Rg = ranks + blockIdx.y;
+  const int t = threadIdx.x;
+  const int W = Rg->world, r = Rg->rank;
+  uint64_t* const* tab = Rg->peer_flag;
+  uint64_t* ep = Rg->epoch;
+  const int64_t spin = Rg->spin_limit;
+  uint64_t* theirs = t < W ? tab[t] : nullptr;
+  uint64_t* mine = tab[r];
+  const uint64_t e = ld_relaxed_sys(ep) + 1;
+  if (t < W) {
+    st_release_sys(theirs + r, e);   // round 0, word [src]
+    if (!wait_flag_ge(mine + t, e, spin)) atomicExch(Rg->status, 1u + t);
+  }
+  __syncwarp();
+  if (t == 0) st_relaxed_sys(ep, e);
 }
 
 // ============================================================ launch helpers
@@ -498,12 +644,13 @@ static int coll_grid(const void* kernel, int64_t work_ctas, int n_ranks, int* gr
   return 0;
 }
 
-static int coll_launch(const void* kernel, int grid, int n_ranks, void** args, cudaStream_t st)
+static int coll_launch(const void* kernel, int grid, int n_ranks, void** args, cudaStream_t st,
+                       int threads = kCollThreads)
 {
   if (n_ranks > 1)
-    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(kCollThreads), args, 0, st));
+    GMT_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid, n_ranks), dim3(threads), args, 0, st));
   else
-    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(kCollThreads), args, 0, st));
+    GMT_CUDA(cudaLaunchKernel(kernel, dim3(grid, 1), dim3(threads), args, 0, st));
   return 0;
 }
 
@@ -516,7 +663,17 @@ int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, in
 {
   using namespace gmt;
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_allgather_f64: bad argument");
+  GMT_REQUIRE(use_multicast >= 0 && use_multicast <= 4, GMT_EINVAL, "gmt_allgather_f64: unknown mode %d", use_multicast);
   int grid = 0, root = -1;
+  if (use_multicast == 2) {   // LL cells
+    GMT_REQUIRE(n <= kLLGatherMax, GMT_ETOOBIG, "gmt_allgather_f64: LL mode is for slices of up to %lld doubles",
+                (long long)kLLGatherMax);
+    const void* kl = (const void*)gather_ll_kernel;
+    int rc = coll_grid(kl, (n + kCollThreads - 1) / kCollThreads, n_ranks, &grid);
+    if (rc) return rc;
+    void* largs[] = {(void*)&ranks_dev, (void*)&n, (void*)&from_in};
+    return coll_launch(kl, grid, n_ranks, largs, as_stream(stream));
+  }
   const void* k = (const void*)gather_kernel;
   int rc = coll_grid(k, (n / 4 + kCollThreads - 1) / kCollThreads + 1, n_ranks, &grid);
   if (rc) return rc;
@@ -559,10 +716,20 @@ int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t
   using namespace gmt;
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n >= 0, GMT_EINVAL, "gmt_daxpy_allreduce_f64: bad argument");
   const void* k = (const void*)daxpy_allreduce_kernel;
-  int grid = 0;
-  int rc = coll_grid(k, (n / 4 + kDaChunk - 1) / kDaChunk, n_ranks, &grid);
-  if (rc) return rc;
-  void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&a};
+  // one chunk per CTA in address order; beyond kDaMaxCtas chunks (or the co-resident share of a
+  // cooperative multi-rank launch) every CTA takes several consecutive chunks
+  const int64_t nchunks = std::max<int64_t>(1, (n / 4 + kDaChunk - 1) / kDaChunk);
+  int64_t cap = kDaMaxCtas;
+  if (n_ranks > 1) {
+    int g = 0;
+    int rc = coll_grid(k, nchunks, n_ranks, &g);
+    if (rc) return rc;
+    cap = std::min<int64_t>(cap, g);
+  }
+  GMT_REQUIRE((nchunks + cap - 1) / cap < (1LL << 31), GMT_ETOOBIG, "gmt_daxpy_allreduce_f64: n too large");
+  int per_cta = (int)((nchunks + cap - 1) / cap);
+  int grid = (int)((nchunks + per_cta - 1) / per_cta);
+  void* args[] = {(void*)&ranks_dev, (void*)&n, (void*)&a, (void*)&per_cta};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));
 }
 
@@ -575,9 +742,8 @@ int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int6
   GMT_REQUIRE(axis == 0 || axis == 1, GMT_EINVAL, "gmt_axis_sum_allreduce_f64: axis must be 0 or 1");
   GMT_REQUIRE(n_out >= 0 && n_out <= (axis == 0 ? ny : nx), GMT_EINVAL,
               "gmt_axis_sum_allreduce_f64: n_out exceeds the surviving extent");
-  // LL cells (16 bytes per double per peer) while the vector is small, one-shot beyond
-  const void* k = n_out <= kLLMaxDoubles ? (const void*)axis_sum_allreduce_kernel<3>
-                                         : (const void*)axis_sum_allreduce_kernel<0>;
+  // (LL cells while n_out x world is small, one-shot beyond: decided in the kernel, which knows the world size)
+  const void* k = (const void*)axis_sum_allreduce_kernel;
   int grid = 0;
   const int64_t work = axis == 0 ? (n_out + kCollThreads / 32 - 1) / (kCollThreads / 32) : (n_out + 31) / 32;
   int rc = coll_grid(k, work, n_ranks, &grid);
@@ -586,12 +752,22 @@ int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int6
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));
 }
 
+size_t gmt_coll_stage_bytes(int world, int64_t stage_cap)
+{
+  if (world < 1 || stage_cap < 1) return 0;
+  // 2 input + 2 result vectors (parity double-buffered) and 2 x world x stage_cap 16-byte LL cells
+  return size_t(4 + 4 * (int64_t)world) * size_t(stage_cap) * sizeof(double);
+}
+
+int64_t gmt_coll_min_stage_cap(void) { return gmt::kDaMaxCtas; }
+int64_t gmt_coll_ll_gather_max(void) { return gmt::kLLGatherMax; }
+
 int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream)
 {
   using namespace gmt;
   GMT_REQUIRE(ranks_dev && n_ranks >= 1, GMT_EINVAL, "gmt_barrier: bad argument");
   void* args[] = {(void*)&ranks_dev};
-  return coll_launch((const void*)barrier_kernel, 1, n_ranks, args, as_stream(stream));
+  return coll_launch((const void*)barrier_kernel, 1, n_ranks, args, as_stream(stream), 32);
 }
 
 }  // extern "C"

@@ -135,6 +135,10 @@ int gmt_engine2d_create(int px, int py, const int* devices, int64_t nx, int64_t 
   // domain [0, 8) in each decomposed direction, weak scaling: the per-rank tile is fixed
   // (mpi_stencil2d_gt.cc:395,427-431)
   e->dx = 8.0 / double(nx * px), e->dy = 8.0 / double(ny * py);
+  // slab decompositions are the reference's tests: ONE spacing, that of the differentiated axis,
+  // is used for both coordinates (delta = 8 / n_global_deriv, mpi_stencil2d_gt.cc:427-448)
+  if (gx && !gy) e->dy = e->dx;
+  if (gy && !gx) e->dx = e->dy;
   e->sx = gx ? 1.0 / e->dx : 0.0, e->sy = gy ? 1.0 / e->dy : 0.0;
   e->ranks.resize(world);
 
@@ -305,6 +309,20 @@ int gmt_engine2d_step(gmt_engine2d* e)
   return 0;
 }
 
+int gmt_engine2d_exchange(gmt_engine2d* e)
+{
+  DeviceRestore restore_;
+  GMT_REQUIRE(e, GMT_EINVAL, "gmt_engine2d_exchange: NULL engine");
+  // the halo exchange alone (boundary_exchange_x/_y, mpi_stencil2d_gt.cc:136-373): one small kernel per GPU
+  const int rc = e->exec->run([e](int i) {
+    DeviceGroup& g = e->groups[i];
+    return gmt_halo_exchange2d_f64(g.desc, (int)g.ranks.size(), e->nx, e->ny, e->gx, e->gy, g.stream);
+  });
+  if (rc) return rc;
+  ++e->steps;
+  return 0;
+}
+
 int gmt_engine2d_synchronize(gmt_engine2d* e)
 {
   DeviceRestore restore_;
@@ -334,20 +352,34 @@ int gmt_engine2d_status(gmt_engine2d* e, int* first_bad_rank)
   return 0;
 }
 
+static int time_calls(gmt_engine2d* e, int (*call)(gmt_engine2d*), int steps, int warmup, double* ms_per_step);
+
 int gmt_engine2d_time_steps(gmt_engine2d* e, int steps, int warmup, double* ms_per_step)
 {
-  DeviceRestore restore_;
   GMT_REQUIRE(e && ms_per_step && steps > 0 && warmup >= 0, GMT_EINVAL, "gmt_engine2d_time_steps: bad arguments");
+  return time_calls(e, gmt_engine2d_step, steps, warmup, ms_per_step);
+}
+
+int gmt_engine2d_time_exchanges(gmt_engine2d* e, int steps, int warmup, double* ms_per_exchange)
+{
+  GMT_REQUIRE(e && ms_per_exchange && steps > 0 && warmup >= 0, GMT_EINVAL,
+              "gmt_engine2d_time_exchanges: bad arguments");
+  return time_calls(e, gmt_engine2d_exchange, steps, warmup, ms_per_exchange);
+}
+
+static int time_calls(gmt_engine2d* e, int (*call)(gmt_engine2d*), int steps, int warmup, double* ms_per_step)
+{
+  DeviceRestore restore_;
   int rc = 0;
   for (int i = 0; i < warmup; ++i)
-    if ((rc = gmt_engine2d_step(e)) != 0) return rc;
+    if ((rc = call(e)) != 0) return rc;
   if ((rc = gmt_engine2d_synchronize(e)) != 0) return rc;
   for (auto& g : e->groups) {
     GMT_CUDA(cudaSetDevice(g.device));
     GMT_CUDA(cudaEventRecord(g.ev0, g.stream));
   }
   for (int i = 0; i < steps; ++i)
-    if ((rc = gmt_engine2d_step(e)) != 0) return rc;
+    if ((rc = call(e)) != 0) return rc;
   for (auto& g : e->groups) {
     GMT_CUDA(cudaSetDevice(g.device));
     GMT_CUDA(cudaEventRecord(g.ev1, g.stream));

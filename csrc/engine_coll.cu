@@ -101,7 +101,8 @@ int gmt_coll_engine_create(int world, const int* devices, int64_t buf_doubles, i
   gmt_coll_engine* e = new gmt_coll_engine;
   e->world = world;
   e->buf_doubles = std::max<int64_t>(buf_doubles, 4);
-  e->stage_cap = std::max<int64_t>(stage_cap, 8);
+  // at least 2048 cells per source rank: daxpy + global sum stores one partial per CTA (up to 2048)
+  e->stage_cap = std::max<int64_t>(stage_cap, gmt_coll_min_stage_cap());
   e->spin_limit = spin_limit;
   e->ranks.resize(world);
   e->group_of.resize(world), e->slot_of.resize(world);
@@ -143,7 +144,7 @@ int gmt_coll_engine_create(int world, const int* devices, int64_t buf_doubles, i
   for (int r = 0; r < world; ++r) {
     CollRankMem& m = e->ranks[r];
     size_t cur = 0;
-    m.off_stage = take(cur, size_t(4 + 4 * world) * e->stage_cap * 8);   // vectors + LL cells
+    m.off_stage = take(cur, gmt_coll_stage_bytes(world, e->stage_cap));   // vectors + LL cells
     m.off_flags = take(cur, size_t(GMT_COLL_FLAG_WORDS) * 8);
     m.off_epoch = take(cur, 64), m.off_done = take(cur, 64), m.off_status = take(cur, 64);
     m.off_scratch = take(cur, scratch_bytes);
@@ -256,7 +257,9 @@ int gmt_coll_engine_allgather(gmt_coll_engine* e, int64_t n, int from_in)
               "buffer of %lld doubles cannot hold %d slices of %lld", (long long)e->buf_doubles, e->world,
               (long long)n);
   return for_each_group(e, [&](CollGroup& g) {
-    return gmt_allgather_f64(g.desc, (int)g.ranks.size(), n, from_in, 0, g.stream);
+    // slices up to 64 KiB travel as LL cells (one one-way trip, no signalling rounds)
+    const int mode = (e->world > 1 && n <= std::min<int64_t>(e->stage_cap, gmt_coll_ll_gather_max())) ? 2 : 0;
+    return gmt_allgather_f64(g.desc, (int)g.ranks.size(), n, from_in, mode, g.stream);
   });
 }
 

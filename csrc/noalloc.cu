@@ -114,8 +114,12 @@ __global__ void __launch_bounds__(kNoAllocThreads, 2)
   if (threadIdx.x == 0) *out_sum = total;
 }
 
-// Device address of the scratch on the current device, looked up once per device.
-static int noalloc_scratch_ptr(unsigned char** out)
+// Device address of the scratch on the current device, looked up once per device.  The look-up
+// (which may load the module on that device) must not happen inside a stream capture: a first call
+// on a capturing stream is refused with a clear message instead of failing somewhere in the runtime.
+// The address is cached for the life of the process; a cudaDeviceReset() in the host program
+// invalidates it (and everything else this library holds on that device).
+static int noalloc_scratch_ptr(unsigned char** out, cudaStream_t st)
 {
   static std::mutex mu;
   static unsigned char* ptrs[kMaxDevices] = {nullptr};
@@ -124,6 +128,11 @@ static int noalloc_scratch_ptr(unsigned char** out)
   GMT_REQUIRE(dev >= 0 && dev < kMaxDevices, GMT_EUNSUPPORTED, "gmt_daxpy_sum_noalloc_f64: device ordinal %d not supported", dev);
   std::lock_guard<std::mutex> lock(mu);
   if (ptrs[dev] == nullptr) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    GMT_CUDA(cudaStreamIsCapturing(st, &cap));
+    GMT_REQUIRE(cap == cudaStreamCaptureStatusNone, GMT_EUNSUPPORTED,
+                "gmt_daxpy_sum_noalloc_f64: the first call on device %d must come before any stream capture "
+                "(it looks up the scratch array's device address)", dev);
     void* p = nullptr;
     // `dev` is current here, so this is the address of THIS device's copy of the array
     GMT_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
@@ -154,7 +163,7 @@ int gmt_daxpy_sum_noalloc_f64(int64_t n, double a, const double* x, double* y, d
               (long long)n, (long long)kNoAllocMaxN);
   cudaStream_t st = as_stream(stream);
   unsigned char* scratch = nullptr;
-  int rc = noalloc_scratch_ptr(&scratch);
+  int rc = noalloc_scratch_ptr(&scratch, st);
   if (rc) return rc;
   // the arrival counter must start at zero; the array still holds the previous call's state
   GMT_CUDA(cudaMemsetAsync(scratch, 0, kNoAllocHeaderBytes, st));

@@ -41,6 +41,21 @@ int stream_counters(cudaStream_t stream, unsigned int** out)
 
 }  // namespace gmt
 
+namespace gmt {
+// Test hook: a kernel that does nothing but hold SM resources for a while.
+__global__ void __launch_bounds__(1024) occupy_kernel(unsigned long long ns)
+{
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t - t0 >= ns) break;
+    __nanosleep(1000);
+  }
+}
+}  // namespace gmt
+
 extern "C" {
 
 const char* gmt_last_error(void) { return gmt::err_buf(); }
@@ -252,6 +267,14 @@ int gmt_ipc_open_handle(const unsigned char handle[64], void** out)
 int gmt_ipc_close_handle(void* mapped)
 {
   GMT_CUDA(cudaIpcCloseMemHandle(mapped));
+  return 0;
+}
+
+int gmt_debug_occupy(int ctas, unsigned long long ns, gmt_stream_t stream)
+{
+  GMT_REQUIRE(ctas >= 1, GMT_EINVAL, "gmt_debug_occupy: ctas must be positive");
+  gmt::occupy_kernel<<<ctas, 1024, 0, gmt::as_stream(stream)>>>(ns);
+  GMT_LAUNCH_CHECK();
   return 0;
 }
 

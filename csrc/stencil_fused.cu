@@ -170,42 +170,57 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
 // computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
 // each followed by its own fence + flag, so the exchange streams underneath the sweep: the
 // export front moves ~10x faster than the compute front.
+// x-face chunks are exported in groups when there are many of them: the system-scope fence that
+// precedes a flag waits for the round trip of every store before it, so one fence per 1024-column
+// chunk (2 x 512 of them in the reference's dim-0 tile) kept each exporting CTA busy for ~4 us per
+// chunk; four chunks share one fence there.  Few chunks (the 16384^2 grid tile: 16 per side) keep
+// one fence each, so the first flags leave as early as possible.
+constexpr int kPushGroup = 4;
+constexpr int64_t kPushGroupMin = 64;  // group only when a side has at least this many chunks
+
 template <int GX, int GY, bool kDebug, bool kNamedBar = false>
-__device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i)
+__device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i,
+                                           int max_push_ctas = 32)
 {
   const int tid = threadIdx.x;
   const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
-  constexpr int kPushCtas = 32;
   const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
   const int64_t nfy = GY ? tiles_i : 0;
-  const int64_t nunits = 2 * (nfx + nfy);
-  const int npush = min((int)gridDim.x, kPushCtas);
+  const int grp = nfx >= kPushGroupMin ? kPushGroup : 1;
+  const int64_t ngx = (nfx + grp - 1) / grp;
+  const int64_t nunits = 2 * (ngx + nfy);
+  const int npush = min((int)gridDim.x, max_push_ctas);
   if ((int)blockIdx.x >= npush) return;
   for (int64_t u = blockIdx.x; u < nunits; u += npush) {
     int side;
-    int64_t c;
-    if (u < 2 * nfx) {
+    int64_t c, c_end;
+    if (u < 2 * ngx) {
       side = (int)(u & 1);
-      c = u >> 1;
+      c = (u >> 1) * grp;
+      c_end = min(nfx, c + grp);
     } else {
-      side = 2 + (int)((u - 2 * nfx) & 1);
-      c = (u - 2 * nfx) >> 1;
+      side = 2 + (int)((u - 2 * ngx) & 1);
+      c = (u - 2 * ngx) >> 1;
+      c_end = c + 1;
     }
     if (R.has[side] != 1) continue;  // CTA-uniform; 2 = fed by the host, nothing to export
     double* box = R.peer_inbox[side][par];
     if (side < 2) {
-      const int64_t j0 = c * kFlagCols;
       const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
-      double2 v[kFlagCols / kStThreads];
+#pragma unroll 1
+      for (int64_t cc = c; cc < c_end; ++cc) {
+        const int64_t j0 = cc * kFlagCols;
+        double2 v[kFlagCols / kStThreads];
 #pragma unroll
-      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-        const int64_t j = j0 + tid + q * kStThreads;
-        if (j < ny) v[q] = ldg128(src + j * ldz);
-      }
+        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+          const int64_t j = j0 + tid + q * kStThreads;
+          if (j < ny) v[q] = ldg128(src + j * ldz);
+        }
 #pragma unroll
-      for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-        const int64_t j = j0 + tid + q * kStThreads;
-        if (j < ny) stg128(box + 2 * j, v[q]);
+        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
+          const int64_t j = j0 + tid + q * kStThreads;
+          if (j < ny) stg128(box + 2 * j, v[q]);
+        }
       }
     } else {
       const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
@@ -228,8 +243,10 @@ __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e,
       __syncthreads();
     if (tid == 0) {
       fence_sys();
-      if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
-      st_release_sys(R.peer_flag[side] + c, e);
+      for (int64_t cc = c; cc < c_end; ++cc) {
+        if (kDebug) debug_delay(e * 8191 + (uint64_t)(u + cc) * 31 + blockIdx.y);
+        st_release_sys(R.peer_flag[side] + cc, e);
+      }
     }
   }
 }
@@ -464,6 +481,85 @@ __global__ void __launch_bounds__(kStThreads + 32, 2)
   finish_epoch(R.done, R.epoch, e, 2);
 }
 
+// ====================================================================== exchange only
+// The reference's central callable -- boundary_exchange (mpi_stencil_gt.cc:83-122),
+// boundary_exchange_x / _y (mpi_stencil2d_gt.cc:136-373) -- and the quantity it times
+// (mpi_stencil_gt.cc:200-204, mpi_stencil2d_gt.cc:512-522), as one small kernel per rank on the
+// same inboxes, flags and epochs as the fused steps: export the boundary values into the
+// neighbours' inboxes, wait for theirs, put them into the array's own ghost cells.  No sweep;
+// afterwards the array is what it is after the reference's exchange, ready for ANY compute step.
+// Exchange-only calls and fused steps can be mixed freely on one plan (each advances the epoch).
+// Every CTA exports all of its share before it waits for anything, and waits only for another
+// rank's exports, so the kernel cannot block itself whatever part of the grid is resident.
+template <bool kDebug>
+__global__ void __launch_bounds__(64) halo_exchange1d_kernel(const gmt_halo1d_rank* __restrict__ ranks)
+{
+  __shared__ gmt_halo1d_rank R;
+  load_rank(R, ranks + blockIdx.y);
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int tid = threadIdx.x;
+  if (tid == 0 || tid == 32) {
+    const int s = tid >> 5;  // 0: low neighbour, 1: high neighbour
+    if (R.has[s]) {
+      stg128(R.peer_inbox[s][par], ldg128(s == 0 ? R.z + 2 : R.z + R.n));
+      fence_sys();
+      if (kDebug) debug_delay(e * 131 + blockIdx.y * 7 + s);
+      st_release_sys(R.peer_flag[s], e);
+      if (!wait_flag_ge(R.my_flag[s], e, R.spin_limit)) atomicExch(R.status, 1u + s);
+      stg128(s == 0 ? R.z : R.z + R.n + 2, ld_peer_f64x2(R.my_inbox[s][par]));
+    }
+  }
+  finish_epoch(R.done, R.epoch, e, 2);
+}
+
+template <int GX, int GY, bool kDebug>
+__global__ void __launch_bounds__(kStThreads, 2) halo_exchange2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
+{
+  __shared__ gmt_halo2d_rank R;
+  load_rank(R, ranks + blockIdx.y);
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int tid = threadIdx.x;
+  const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
+  const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
+  push_faces<GX, GY, kDebug>(R, e, par, tiles_i, (int)gridDim.x);   // every CTA exports
+  // landing units: (side, chunk) pairs in the same enumeration as the flags
+  const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
+  const int64_t nfy = GY ? tiles_i : 0;
+  const int64_t nunits = 2 * (nfx + nfy);
+  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+    int side;
+    int64_t c;
+    if (u < 2 * nfx) {
+      side = (int)(u & 1);
+      c = u >> 1;
+    } else {
+      side = 2 + (int)((u - 2 * nfx) & 1);
+      c = (u - 2 * nfx) >> 1;
+    }
+    if (!R.has[side]) continue;  // physical side without a host feed: ghosts stay as they are
+    if (tid == 0) {
+      if (!wait_flag_ge(R.my_flag[side] + c, e, R.spin_limit)) atomicExch(R.status, 1u + side);
+    }
+    __syncthreads();
+    const double* box = R.my_inbox[side][par];
+    if (side < 2) {
+      const int64_t j0 = c * kFlagCols, j1 = min(ny, j0 + (int64_t)kFlagCols);
+      double* dst = R.z + (side == 0 ? 0 : nx + 2) + GY * ldz;
+      for (int64_t j = j0 + tid; j < j1; j += kStThreads) stg128(dst + j * ldz, ld_peer_f64x2(box + 2 * j));
+    } else {
+      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+      double* dst = R.z + GX + (side == 2 ? 0 : ny + 2) * ldz;
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+        for (int64_t i = i0 + 2 * tid; i < i1; i += 2 * kStThreads)
+          stg128(dst + i + r * ldz, ld_peer_f64x2(box + r * nx + i));
+    }
+  }
+  finish_epoch(R.done, R.epoch, e, 2);
+}
+
 // flags[i] <- *epoch + 1 with release semantics: "the host-fed ghost values of the step now
 // running are in the inbox".  Runs on the stream that carried the host-to-device copy, next to
 // the fused kernel of that step (which bumps *epoch only when it finishes, i.e. after it has
@@ -557,6 +653,48 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   const bool ws = gx && !gy && !oneshot;
   const int tj_flags = tj | ((!ws && !(ord && ord[0] == 'i')) ? (1 << 16) : 0);
   return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj_flags, threads, oneshot);
+}
+
+int gmt_halo_exchange1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1, GMT_EINVAL, "gmt_halo_exchange1d_f64: bad argument");
+  const void* k = g_debug_push_delay_host ? (const void*)halo_exchange1d_kernel<true> : (const void*)halo_exchange1d_kernel<false>;
+  void* args[] = {(void*)&ranks_dev};
+  if (n_ranks > 1)
+    GMT_CUDA(cudaLaunchCooperativeKernel(k, dim3(1, n_ranks), dim3(64), args, 0, as_stream(stream)));
+  else
+    GMT_CUDA(cudaLaunchKernel(k, dim3(1, 1), dim3(64), args, 0, as_stream(stream)));
+  return 0;
+}
+
+int gmt_halo_exchange2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny, int gx, int gy,
+                            gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && nx > 0 && ny > 0, GMT_EINVAL, "gmt_halo_exchange2d_f64: bad argument");
+  GMT_REQUIRE((gx == 0 || gx == 2) && (gy == 0 || gy == 2) && (gx || gy), GMT_EINVAL,
+              "gmt_halo_exchange2d_f64: ghost widths must be 0 or 2 and not both 0");
+  GMT_REQUIRE(nx % 4 == 0, GMT_EUNSUPPORTED, "gmt_halo_exchange2d_f64: nx must be a multiple of 4");
+  const bool dbg = g_debug_push_delay_host != 0;
+  const void* k = nullptr;
+#define GMT_PICKX(GX_, GY_) (dbg ? (const void*)halo_exchange2d_kernel<GX_, GY_, true> : (const void*)halo_exchange2d_kernel<GX_, GY_, false>)
+  if (gx && gy) k = GMT_PICKX(2, 2);
+  else if (gx) k = GMT_PICKX(2, 0);
+  else k = GMT_PICKX(0, 2);
+#undef GMT_PICKX
+  // one landing unit per (side, 1024-column chunk | 1024-row block); a face of a few chunks needs a
+  // few CTAs, the reference's 8 MiB strided faces (2 x 512 chunks) fill the GPU
+  const int64_t units = 2 * ((gx ? gmt_halo2d_flag_count(0, nx, ny) : 0) + (gy ? gmt_halo2d_flag_count(2, nx, ny) : 0));
+  int grid = 0;
+  int rc = persistent_grid(k, kStThreads, units, n_ranks, &grid);
+  if (rc) return rc;
+  void* args[] = {(void*)&ranks_dev};
+  if (n_ranks > 1)
+    GMT_CUDA(cudaLaunchCooperativeKernel(k, dim3(grid, n_ranks), dim3(kStThreads), args, 0, as_stream(stream)));
+  else
+    GMT_CUDA(cudaLaunchKernel(k, dim3(grid, 1), dim3(kStThreads), args, 0, as_stream(stream)));
+  return 0;
 }
 
 int gmt_publish_epoch_flags(uint64_t* flags, int64_t n, const uint64_t* epoch, gmt_stream_t stream)

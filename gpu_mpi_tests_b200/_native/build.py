@@ -62,6 +62,20 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     nvcc = find_nvcc()
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     hdr_m = _headers_mtime()
+    if LIB.exists() and not force and MANIFEST.exists() and is_stale():
+        # contents changed: trust hashes over mtimes for the objects whose source differs
+        import json
+        try:
+            old = json.loads(MANIFEST.read_text())
+        except ValueError:
+            old = {}
+        new = _fingerprint()
+        changed = {k for k in new if old.get(k) != new[k]}
+        if any(not k.endswith(".cu") for k in changed):
+            force = True           # a header or the flags changed: everything is stale
+        else:
+            for k in changed:
+                (OBJ_DIR / (Path(k).stem + ".o")).unlink(missing_ok=True)
     jobs = []
     objs = []
     for src in sources():
@@ -74,12 +88,19 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(lambda so: _compile(nvcc, so[0], so[1], verbose), jobs))
     if jobs or not LIB.exists():
-        cmd = [nvcc, "-shared", "-o", str(LIB), *map(str, objs), "-lcudart", "-ldl"]
+        # link under a temporary name and rename: a rank that looks for the library while the link
+        # is running must see the old file or the new one, never a partial one
+        tmp = LIB.with_name(f".{LIB.name}.{os.getpid()}.tmp")
+        cmd = [nvcc, "-shared", "-o", str(tmp), *map(str, objs), "-lcudart", "-ldl"]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
+            tmp.unlink(missing_ok=True)
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+        os.replace(tmp, LIB)
         if verbose:
             sys.stderr.write(f"[build] linked {LIB}\n")
+    import json
+    MANIFEST.write_text(json.dumps(_fingerprint(), indent=0))
     build_programs(nvcc, verbose)
     return LIB
 
@@ -110,19 +131,49 @@ def build_programs(nvcc: str | None = None, verbose: bool = False) -> list[Path]
     return built
 
 
+MANIFEST = OUT_DIR / "build_manifest.json"
+
+
+def _fingerprint() -> dict:
+    """Content hashes of everything the library is built from (mtimes do not survive every copy of
+    the tree, contents do)."""
+    import hashlib
+    files = sources() + sorted(CSRC.glob("*.h")) + sorted(CSRC.glob("*.cuh")) + sorted((ROOT / "include").glob("*.h"))
+    out = {str(f.relative_to(ROOT)): hashlib.sha256(f.read_bytes()).hexdigest() for f in files}
+    out["flags"] = " ".join(NVCC_FLAGS + os.environ.get("GMT_NVCC_EXTRA", "").split())
+    return out
+
+
+def is_stale() -> bool:
+    """True when the library is missing or was built from other sources than the tree holds now."""
+    import json
+    if not LIB.exists():
+        return True
+    try:
+        return json.loads(MANIFEST.read_text()) != _fingerprint()
+    except (OSError, ValueError):
+        return True
+
+
 def ensure_built() -> Path:
-    """Build the library and the programs if the tree has none (a fresh checkout: build outputs are
-    git-ignored).  Safe to call from every rank of a multi-process launch: an exclusive file lock
-    lets one process build while the others wait and then find the result."""
+    """Bring the library and the programs up to date with the sources (a fresh checkout has none:
+    build outputs are git-ignored; after an edit of csrc/ or include/ the stale objects are
+    recompiled).  Safe to call from every rank of a multi-process launch: the exclusive file lock is
+    taken FIRST, so one process builds while the others wait and then find nothing left to do.
+    Without a compiler an existing library is used as it is."""
     import fcntl
-    if LIB.exists():
-        return LIB
     OUT_DIR.mkdir(parents=True, exist_ok=True)
     with open(OUT_DIR / ".build.lock", "w") as lock:
         fcntl.flock(lock, fcntl.LOCK_EX)
         try:
-            if not LIB.exists():
-                build()
+            if is_stale():
+                try:
+                    build()
+                except RuntimeError:
+                    if not LIB.exists():
+                        raise
+                    sys.stderr.write("[build] WARNING: sources are newer than libgmt_b200.so and rebuilding failed; "
+                                     "using the existing library\n")
         finally:
             fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB

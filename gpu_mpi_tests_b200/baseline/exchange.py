@@ -129,7 +129,8 @@ class BaselineStencil1D:
 
 class BaselineStencil2D:
     def __init__(self, rt: "_rt.Runtime", px: int, py: int, nx: int, ny: int, gx: int, gy: int,
-                 stage: str = "device", mem_space: str = "device", variant: str = "vector"):
+                 stage: str = "device", mem_space: str = "device", variant: str = "vector",
+                 dx: float | None = None, dy: float | None = None):
         if px * py != rt.world_size:
             raise ValueError(f"grid {px}x{py} does not match world {rt.world_size}")
         if stage not in ("device", "none", "host"):
@@ -138,8 +139,11 @@ class BaselineStencil2D:
         self.stage, self.mem_space, self.variant = stage, mem_space, variant
         self.device = rt.device
         self.grid = decomp.Grid2D(px, py, rt.rank)
-        self.dx = DOMAIN / (nx * px)
-        self.dy = DOMAIN / (ny * py)
+        # slab decompositions use the reference's single spacing (mpi_stencil2d_gt.cc:427-448)
+        dflt_x = DOMAIN / (nx * px) if (gx or not gy) else DOMAIN / (ny * py)
+        dflt_y = DOMAIN / (ny * py) if (gy or not gx) else DOMAIN / (nx * px)
+        self.dx = dx if dx is not None else dflt_x
+        self.dy = dy if dy is not None else dflt_y
         self.sx = 1.0 / self.dx if gx else 0.0
         self.sy = 1.0 / self.dy if gy else 0.0
         r = rt.rank

@@ -9,10 +9,12 @@ spent exchanging over n_iter iterations, and of err_norm), then 4 all-reduce lin
                   unpack with the same staging meaning of `buf` (dim 0: host staging on top of
                   device staging; dim 1: device staging vs zero-copy), host-clock timing of the
                   exchange only, stencil untimed.
---impl fused      one kernel per iteration does exchange + stencil; the printed "exchange"
-                  seconds are the fused iterations minus the same sweep without neighbours
-                  (device-timed), i.e. the exposed cost of the exchange.  `buf` has no meaning
-                  (there are no staging buffers) but all 8 lines are printed.
+--impl fused      the printed seconds are n_iter calls of the peer-memory exchange alone
+                  (gmt_halo_exchange2d_f64: export, flags, landing; device-timed), the quantity
+                  the reference times.  The product's step fuses that exchange into the stencil
+                  kernel; its seconds, and what the exchange still costs when hidden under the
+                  sweep (fused minus plain sweep), go to the --jsonl record (fused_s, exposed_s).
+                  `buf` has no meaning (there are no staging buffers) but all 8 lines are printed.
 The all-reduce lines time the in-place SUM of n_local_deriv doubles (8 KiB by default): the
 fused path runs axis-sum + all-reduce as one kernel (device-timed), the baseline path times the
 library all_reduce alone with the host clock, as the reference does."""
@@ -46,6 +48,7 @@ def test_deriv(rt, out, impl, space, dim, mem, use_buffers, n_local_deriv, n_oth
     wl.setup()
     r = rt.rank
     total = 0.0
+    extra = {}
     if impl == "baseline":
         for i in range(n_warmup + n_iter):
             t0 = time.perf_counter()
@@ -57,22 +60,9 @@ def test_deriv(rt, out, impl, space, dim, mem, use_buffers, n_local_deriv, n_oth
             if rt.is_cuda:
                 torch.cuda.synchronize()
     else:
-        for _ in range(n_warmup):
-            wl.step()
-        torch.cuda.synchronize()
-        rt.barrier()
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        e0.record()
-        for _ in range(n_iter):
-            wl.step()
-        e1.record()
-        z, o = wl.z[r], wl.out[r]
-        for _ in range(n_iter):
-            local.stencil2d(z, dim, wl.sx if dim == 0 else wl.sy, out=o)
-        e2.record()
-        torch.cuda.synchronize()
-        total = max(0.0, (e0.elapsed_time(e1) - e1.elapsed_time(e2)) * 1e-3)
-        wl.step()
+        m = wl.measure_fused(n_iter, n_warmup)
+        total = m["exchange_s"]
+        extra = {"fused_s": m["fused_s"], "plain_s": m["plain_s"], "exposed_s": m["exposed_s"]}
     err = wl.err_norm(r)
     wl.check()
     if debug:
@@ -83,7 +73,7 @@ def test_deriv(rt, out, impl, space, dim, mem, use_buffers, n_local_deriv, n_oth
     if r == 0:
         out(report.test_deriv_line(dim, mem, use_buffers, time_sum, err_sum))
     _common.record_append("tests", {"test": "deriv", "dim": dim, "space": mem, "buf": int(use_buffers), "n_iter": n_iter,
-                                    "exchange_s": total, "err_norm": err,
+                                    "exchange_s": total, "err_norm": err, **extra,
                                     "exchange_s_sum": time_sum if r == 0 else None, "err_sum": err_sum if r == 0 else None})
     del wl
     if rt.is_cuda:

@@ -75,6 +75,7 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
     if debug:
         debug_dump_boundary_rows(rt, wl.z[r])
     total = 0.0
+    extra = {}
     if impl == "baseline":
         for i in range(n_warmup + n_iter):
             t0 = time.perf_counter()
@@ -86,21 +87,11 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
             if rt.is_cuda:
                 torch.cuda.synchronize()
     else:
-        for _ in range(n_warmup):
-            wl.step()
-        torch.cuda.synchronize()
-        rt.barrier()
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        e0.record()
-        for _ in range(n_iter):
-            wl.step()
-        e1.record()
-        for _ in range(n_iter):
-            local.stencil2d(wl.z[r], 0, wl.sx, out=wl.out[r])
-        e2.record()
-        torch.cuda.synchronize()
-        total = max(0.0, (e0.elapsed_time(e1) - e1.elapsed_time(e2)) * 1e-3)
-        wl.step()
+        # the printed time is the peer-memory exchange alone (device-timed), as in the reference
+        # (mpi_stencil2d_sycl.cc:515-520); fused-step and exposed-cost seconds go to --jsonl
+        m = wl.measure_fused(n_iter, n_warmup)
+        total = m["exchange_s"]
+        extra = {"fused_s": m["fused_s"], "plain_s": m["plain_s"], "exposed_s": m["exposed_s"]}
     if debug:
         if rt.is_cuda:
             torch.cuda.synchronize()
@@ -109,7 +100,7 @@ def run_dim0(rt, out, impl, nx_local, ny, n_iter, n_warmup, stage_host, line_sty
     err = wl.err_norm(r)
     wl.check()
     from . import _common as _c
-    _c.record(nx_local=nx_local, ny=ny, n_iter=n_iter, stage_host=bool(stage_host), exchange_ms=ms, err_norm=err)
+    _c.record(nx_local=nx_local, ny=ny, n_iter=n_iter, stage_host=bool(stage_host), exchange_ms=ms, err_norm=err, **extra)
     if line_style == "sycl":
         out(report.exchange_time_ms(r, W, ms))
         out(report.err_norm_line(r, W, rt.device_id, rt.vendor_id, err))

@@ -46,7 +46,8 @@ class Stencil1DWorkload:
         self.plan.step()
 
     def exchange_only(self) -> None:
-        """Baseline only: the separately timed boundary_exchange of the reference."""
+        """The separately timed boundary_exchange of the reference (mpi_stencil_gt.cc:83-122,200-204):
+        library send/recv on the baseline path, one small peer-memory kernel on the fused path."""
         self.plan.exchange()
 
     def stencil_only(self) -> None:

@@ -47,6 +47,15 @@ class Stencil2DWorkload:
         else:
             raise ValueError("mode must be grid, dim0 or dim1")
         self.nx, self.ny = nx, ny
+        # slab modes are the reference's tests: ONE grid spacing, delta = 8 / n_global_deriv, is used
+        # for both coordinates (mpi_stencil2d_gt.cc:427-448), so the other axis spans
+        # [0, n_other * delta) and err= is dominated by rounding against the large y^2 / x^3 term,
+        # like the reference's.  The process-grid extension keeps [0, 8) in both directions.
+        dx = dy = None
+        if mode == "dim0":
+            dx = dy = DOMAIN / (nx * world)
+        elif mode == "dim1":
+            dx = dy = DOMAIN / (ny * world)
         self.device = self.rt.device if space is None else space.device
         self.stage, self.mem_space = stage, mem_space
         self.launches_per_step = 1
@@ -55,14 +64,15 @@ class Stencil2DWorkload:
                 raise RuntimeError("impl='fused' needs CUDA; use impl='baseline' on the CPU/gloo path")
             self.space = space if space is not None else make_space(self.rt)
             self.plan = FusedStencil2D(self.space, self.px, self.py, nx, ny, self.gx, self.gy, with_err=with_err,
-                                       spin_limit=spin_limit, mem_space=mem_space, host_fed=host_fed)
+                                       spin_limit=spin_limit, mem_space=mem_space, host_fed=host_fed,
+                                       dx=dx, dy=dy)
             self.ranks = self.plan.ranks
             self.z, self.out = self.plan.z, self.plan.out
             self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy
         elif impl == "baseline":
             from ..baseline.exchange import BaselineStencil2D
             self.plan = BaselineStencil2D(self.rt, self.px, self.py, nx, ny, self.gx, self.gy, stage=stage,
-                                          mem_space=mem_space)
+                                          mem_space=mem_space, dx=dx, dy=dy)
             self.ranks = [self.rt.rank]
             self.z, self.out = self.plan.z, self.plan.out
             self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy
@@ -87,6 +97,61 @@ class Stencil2DWorkload:
                 self.plan.publish_host_sides(r)
         self.plan.step()
 
+    def exchange(self) -> None:
+        """The halo exchange alone -- the reference's boundary_exchange_x/_y call and its timed
+        quantity (mpi_stencil2d_gt.cc:136-373,512-522).  Fused impl: one small peer-memory kernel
+        (pack-free export, flags, landing); baseline: pack / library send-recv / unpack."""
+        if self.impl == "fused":
+            if self.host_fed:
+                for r in self.ranks:
+                    self.plan.publish_host_sides(r)
+            self.plan.exchange()
+        else:
+            self.plan.exchange()
+
+    def stencil_only(self) -> None:
+        """The un-fused sweep on whatever the ghost cells hold (the reference's stencil assignment,
+        mpi_stencil2d_gt.cc:530-532)."""
+        if self.impl == "baseline":
+            self.plan.stencil()
+            return
+        for r in self.ranks:
+            z, o = self.z[r], self.out[r]
+            if self.gx and self.gy:
+                local.stencil2d_xy(z, self.sx, self.sy, out=o)
+            elif self.gx:
+                local.stencil2d(z, 0, self.sx, out=o)
+            else:
+                local.stencil2d(z, 1, self.sy, out=o)
+
+    def measure_fused(self, n_iter: int, n_warmup: int = 5) -> dict:
+        """Device-timed seconds (this rank, CUDA events) for n_iter calls of each of: the exchange
+        alone (the quantity the reference prints), the fused exchange+stencil step, and the plain
+        sweep without any exchange; `exposed_s` = fused - plain is what the exchange costs when it
+        is hidden under the sweep."""
+        if self.impl != "fused":
+            raise RuntimeError("measure_fused needs impl='fused'")
+        for _ in range(n_warmup):
+            self.exchange()
+            self.step()
+        torch.cuda.synchronize(self.device)
+        self.rt.barrier()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record()
+        for _ in range(n_iter):
+            self.exchange()
+        ev[1].record()
+        for _ in range(n_iter):
+            self.step()
+        ev[2].record()
+        for _ in range(n_iter):
+            self.stencil_only()
+        ev[3].record()
+        torch.cuda.synchronize(self.device)
+        ex, fu, pl = (ev[i].elapsed_time(ev[i + 1]) * 1e-3 for i in range(3))
+        self.step()   # leave `out` as the fused step computes it
+        return {"exchange_s": ex, "fused_s": fu, "plain_s": pl, "exposed_s": max(0.0, fu - pl)}
+
     def points_per_rank(self) -> int:
         return self.nx * self.ny
 
@@ -96,30 +161,37 @@ class Stencil2DWorkload:
 
     # ------------------------------------------------------------------ end to end
     def _prepare_e2e_host_fed(self) -> None:
-        """host_fed plans: a pinned buffer per hosted rank mirrors plan.hostbox (the kernel's inbox
-        for the host-fed sides), so ONE H2D copy delivers all sides and no scatter kernel is needed."""
+        """host_fed plans: pinned buffers mirror plan.hostbox (the kernel's inbox for the host-fed
+        sides), so ONE H2D copy delivers all sides and no scatter kernel is needed.  Everything the
+        host writes per step exists twice (slots 0/1: boundary values, flag sources, result word) so
+        that the pipelined variant can prepare step s+1 while step s is still in the queue."""
         plan = self.plan
         self._bc_views = {}
-        self._fed = []   # (pinned host buffer, device inbox) per hosted rank that has host-fed sides
+        self._fed = [[], []]   # per slot: (pinned host buffer, device inbox) per hosted rank with host-fed sides
         total = 0
         for r in self.ranks:
             box = plan.hostbox.get(r)
             if box is None:
                 continue
-            h = torch.empty(box.numel(), dtype=F64, pin_memory=True)
-            for (rr, side), (off, cnt, _f) in plan.host_sides.items():
-                if rr == r:
-                    # inbox layouts: x faces [2*j + r] == row-major (ny, 2); y faces [r*nx + i] == (2, nx)
-                    h[off:off + cnt].view(plan.host_side_shape(side)).copy_(plan.ghost_view(rr, side))
-            self._fed.append((h, box))
+            for slot in range(2):
+                h = torch.empty(box.numel(), dtype=F64, pin_memory=True)
+                for (rr, side), (off, cnt, _f) in plan.host_sides.items():
+                    if rr == r:
+                        # inbox layouts: x faces [2*j + r] == row-major (ny, 2); y faces [r*nx + i] == (2, nx)
+                        h[off:off + cnt].view(plan.host_side_shape(side)).copy_(plan.ghost_view(rr, side))
+                self._fed[slot].append((h, box))
             total += box.numel()
         self._bc_total = total
-        self._host_bc = self._fed[0][0] if self._fed else torch.empty(1, dtype=F64, pin_memory=True)
+        self._host_bc = self._fed[0][0][0] if self._fed[0] else torch.empty(1, dtype=F64, pin_memory=True)
         self._err_dev = torch.zeros(len(self.ranks), dtype=F64, device=self.device)
         self._err_host = torch.zeros(len(self.ranks), dtype=F64, pin_memory=True)
+        self._err_host2 = [self._err_host, torch.zeros(len(self.ranks), dtype=F64, pin_memory=True)]
         self._graph = None
+        self._graphs = [None, None]
         self._graph_failed = False
         self._side_stream = torch.cuda.Stream(device=self.device)
+        self._pipe_events = [None, None]
+        self._pipe_calls = 0
 
     def _prepare_e2e(self) -> None:
         """Per-step host input and output: ONE pinned buffer holding this rank's physical-boundary
@@ -162,7 +234,19 @@ class Stencil2DWorkload:
             self._prepare_e2e()
         return self._bc_total * 8, self._err_host.numel() * 8
 
-    def _e2e_body(self) -> None:
+    def host_inputs(self, slot: int | None = None) -> list:
+        """The pinned host buffers a time-stepping user writes a step's physical-boundary values into
+        (one per hosted rank, sides back to back in plan.host_sides order).  host_fed plans have two
+        sets; slot=None picks the one the NEXT step_e2e_pipelined() call will upload."""
+        if self._host_bc is None:
+            self._prepare_e2e()
+        if not self.host_fed:
+            return [self._host_bc]
+        if slot is None:
+            slot = self._pipe_calls % 2
+        return [h for h, _box in self._fed[slot]]
+
+    def _e2e_body(self, slot: int = 0) -> None:
         """Stream-ordered body of one end-to-end step (also what gets captured in a CUDA graph)."""
         if self.host_fed:
             # two branches: the fused kernel starts at once on the main stream and sweeps the
@@ -173,14 +257,14 @@ class Stencil2DWorkload:
             side = self._side_stream
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                for h, box in self._fed:
+                for h, box in self._fed[slot]:
                     box.copy_(h, non_blocking=True)
                 for r in self.ranks:
-                    self.plan.publish_host_sides_by_copy(r)   # copy engine: needs no SM slot
+                    self.plan.publish_host_sides_by_copy(r, slot)   # copy engine: needs no SM slot
             self.plan.step()
             main.wait_stream(side)
             for k, r in enumerate(self.ranks):   # straight from the kernel's result word to pinned memory
-                self._err_host[k:k + 1].copy_(self.err_sumsq(r), non_blocking=True)
+                self._err_host2[slot][k:k + 1].copy_(self.err_sumsq(r), non_blocking=True)
             return
         if self._bc_total:
             self._dev_bc.copy_(self._host_bc, non_blocking=True)          # one H2D for all sides
@@ -191,6 +275,36 @@ class Stencil2DWorkload:
             self._err_dev[k:k + 1].copy_(self.err_sumsq(r))
         self._err_host.copy_(self._err_dev, non_blocking=True)             # one D2H
 
+    def _capture(self, slot: int):
+        """Capture one end-to-end step (slot's host buffers) in a CUDA graph; None when that fails."""
+        steps_before = None
+        try:
+            self._e2e_body(slot)                  # warm-up outside capture
+            torch.cuda.synchronize(self.device)
+            steps_before = self.plan.steps
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._e2e_body(slot)
+            self.plan.steps = steps_before   # capture launched nothing: the device epoch did not move
+            return g
+        except Exception:  # noqa: BLE001 - capture is an optimisation, never a requirement
+            self._graph_failed = True
+            if steps_before is not None:
+                # whatever ran inside the failed capture launched nothing: the host step count
+                # must not run ahead of the device epoch (host-fed flags are published from it)
+                self.plan.steps = steps_before
+            torch.cuda.synchronize(self.device)
+            return None
+
+    def _graphable(self, use_graph: bool) -> bool:
+        return (use_graph and self.device.type == "cuda" and self.impl == "fused" and len(self.ranks) == 1
+                and not self._graph_failed)
+
+    def _result(self, host: torch.Tensor) -> float:
+        if len(self.ranks) == 1:
+            return float(host[0]) ** 0.5
+        return float(host.max().item()) ** 0.5
+
     def step_e2e(self, use_graph: bool = True) -> float:
         """What a time-stepping user calls: upload this step's boundary values from pinned host
         memory, run the fused step, read the error norm back.  Returns the largest err_norm over
@@ -200,34 +314,70 @@ class Stencil2DWorkload:
         if self._host_bc is None:
             self._prepare_e2e()
         cuda = self.device.type == "cuda"
-        graphable = (use_graph and cuda and self.impl == "fused" and len(self.ranks) == 1
-                     and not self._graph_failed)
-        if graphable and self._graph is None:
-            try:
-                self._e2e_body()                      # warm-up outside capture
-                torch.cuda.synchronize(self.device)
-                g = torch.cuda.CUDAGraph()
-                steps_before = self.plan.steps
-                with torch.cuda.graph(g):
-                    self._e2e_body()
-                self.plan.steps = steps_before   # capture launched nothing: the device epoch did not move
-                self._graph = g
-            except Exception:  # noqa: BLE001 - capture is an optimisation, never a requirement
-                self._graph_failed = True
-                self._graph = None
-                torch.cuda.synchronize(self.device)
-        if graphable and self._graph is not None:
+        if self._graphable(use_graph) and self._graph is None:
+            self._graph = self._capture(0)
             if self.host_fed:
-                self.plan.refresh_host_epoch()
+                self._graphs[0] = self._graph
+        if self._graphable(use_graph) and self._graph is not None:
+            if self.host_fed:
+                self.plan.refresh_host_epoch(0)
             self._graph.replay()
             self.plan.steps += 1
         else:
-            self._e2e_body()
+            self._e2e_body(0)
         if cuda:
             torch.cuda.current_stream().synchronize()
-        if len(self.ranks) == 1:
-            return float(self._err_host[0]) ** 0.5
-        return float(self._err_host.max().item()) ** 0.5
+        return self._result(self._err_host)
+
+    def step_e2e_pipelined(self):
+        """The same step for a loop that can live with a result that lags ONE step: enqueue this
+        step (upload of its boundary values from the pinned buffers `host_inputs()` returned, fused
+        kernel, copy of its error word to pinned memory) and only then wait for and return the
+        PREVIOUS step's err_norm (None on the first call).  The host round trip -- wake-up after the
+        synchronise, Python, graph launch, ~30 us -- is thereby spent while the GPU already runs the
+        next step, instead of between steps.  Everything the host writes per step exists twice and
+        alternates, so a step that is still in the queue never has its inputs, flag epoch or result
+        word overwritten.  `e2e_flush()` returns the last step's result.  The first call
+        captures the two CUDA graphs (and runs one eager warm-up step for each).  host_fed fused
+        plans only; other plans fall back to the synchronous step_e2e()."""
+        if self._host_bc is None:
+            self._prepare_e2e()
+        if not (self.host_fed and self._graphable(True)):
+            return self.step_e2e()
+        slot = self._pipe_calls % 2
+        if self._graphs[0] is None or self._graphs[1] is None:
+            # first use: capture one graph per slot (each capture is preceded by one eager warm-up step)
+            self.e2e_flush()
+            for k in range(2):
+                if self._graphs[k] is None:
+                    self._graphs[k] = self._capture(k)
+            if self._graphs[0] is None or self._graphs[1] is None:
+                self._graphs = [None, None]
+                return self.step_e2e()
+            self._graph = self._graphs[0]
+        self.plan.refresh_host_epoch(slot)
+        self._graphs[slot].replay()
+        self.plan.steps += 1
+        if self._pipe_events[slot] is None:
+            self._pipe_events[slot] = torch.cuda.Event()
+        self._pipe_events[slot].record()
+        self._pipe_calls += 1
+        prev = slot ^ 1
+        if self._pipe_calls < 2 or self._pipe_events[prev] is None:
+            return None
+        self._pipe_events[prev].synchronize()
+        return self._result(self._err_host2[prev])
+
+    def e2e_flush(self):
+        """Wait for the step enqueued by the last step_e2e_pipelined() call; returns its err_norm
+        (None when nothing is outstanding)."""
+        if not self.host_fed or self._host_bc is None or self._pipe_calls == 0:
+            return None
+        last = (self._pipe_calls - 1) % 2
+        if self._pipe_events[last] is None:
+            return None
+        self._pipe_events[last].synchronize()
+        return self._result(self._err_host2[last])
 
     # ------------------------------------------------------------------ validation
     def analytic(self, rank: int) -> torch.Tensor:
@@ -242,6 +392,58 @@ class Stencil2DWorkload:
 
     def err_norm(self, rank: int) -> float:
         return float(self.err_sumsq(rank).item()) ** 0.5
+
+    def verify_ghosts(self) -> int:
+        """Cross-check of the exchange over real peer memory: change the field (a different factor on
+        every rank), run ONE more step, then compare every ghost cell that faces a neighbour with that
+        neighbour's boundary value, bit for bit.  The neighbours' boundary strips are fetched with a
+        library all_gather (verification only, never timed).  Returns the number of mismatching cells
+        summed over all ranks (0 = every ghost is its neighbour's boundary value)."""
+        import torch.distributed as dist
+        gx, gy, nx, ny = self.gx, self.gy, self.nx, self.ny
+        W = self.px * self.py
+        periodic = bool(getattr(self.plan, "periodic", False))
+        for r in self.ranks:
+            self.z[r][gy:gy + ny, gx:gx + nx].mul_(1.0 + 1e-3 * (r + 1))
+        self.step()
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self.check()
+        L = 2 * max(nx, ny)
+
+        def strips(r):
+            z = self.z[r]
+            t = torch.zeros(4, L, dtype=F64, device=self.device)
+            ys, xs = slice(gy, gy + ny), slice(gx, gx + nx)
+            if gx:
+                t[0, :2 * ny] = z[ys, gx:gx + 2].reshape(-1)          # low-x boundary rows
+                t[1, :2 * ny] = z[ys, nx:nx + 2].reshape(-1)          # high-x boundary rows
+            if gy:
+                t[2, :2 * nx] = z[gy:gy + 2, xs].reshape(-1)          # low-y boundary columns
+                t[3, :2 * nx] = z[ny:ny + 2, xs].reshape(-1)          # high-y boundary columns
+            return t
+
+        if len(self.ranks) == W:
+            everyone = {r: strips(r) for r in self.ranks}
+        else:
+            mine = strips(self.ranks[0])
+            gathered = torch.empty(W, 4, L, dtype=F64, device=self.device)
+            dist.all_gather_into_tensor(gathered, mine)
+            everyone = {r: gathered[r] for r in range(W)}
+        bad = 0
+        for r in self.ranks:
+            g = decomp.Grid2D(self.px, self.py, r, periodic)
+            z = self.z[r]
+            ghosts = [z[gy:gy + ny, 0:2], z[gy:gy + ny, gx + nx:gx + nx + 2], z[0:2, gx:gx + nx],
+                      z[gy + ny:gy + ny + 2, gx:gx + nx]]
+            for side in range(4):
+                nb = g.neighbour(side) if (gx if side < 2 else gy) else -1
+                if nb < 0:
+                    continue
+                mine_g = ghosts[side]
+                theirs = everyone[nb][side ^ 1][:mine_g.numel()].view(mine_g.shape)
+                bad += int((mine_g != theirs).sum().item())
+        return int(self.rt.reduce_scalar(float(bad), "sum")) if len(self.ranks) != W else bad
 
     def check(self) -> None:
         if hasattr(self.plan, "check_status"):

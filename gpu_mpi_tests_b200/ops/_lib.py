@@ -132,8 +132,11 @@ _SIGS = {
                                       c_ptr, c_i64, C.c_int, c_dbl, c_dbl, C.c_int, c_dbl, c_ptr]),
     "gmt_fused_stencil1d_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_fused_stencil2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, C.c_int, c_ptr]),
+    "gmt_halo_exchange1d_f64": (None, [c_ptr, C.c_int, c_ptr]),
+    "gmt_halo_exchange2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),
     "gmt_debug_set_push_delay": (None, [C.c_uint]),
+    "gmt_debug_occupy": (None, [C.c_int, C.c_ulonglong, c_ptr]),
     "gmt_publish_epoch_flags": (None, [c_ptr, c_i64, c_ptr, c_ptr]),
     "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_gather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
@@ -141,6 +144,9 @@ _SIGS = {
     "gmt_daxpy_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_dbl, c_ptr]),
     "gmt_axis_sum_allreduce_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, c_i64, C.c_int, c_i64, c_ptr]),
     "gmt_barrier": (None, [c_ptr, C.c_int, c_ptr]),
+    "gmt_coll_stage_bytes": (C.c_size_t, [C.c_int, c_i64]),
+    "gmt_coll_min_stage_cap": (c_i64, []),
+    "gmt_coll_ll_gather_max": (c_i64, []),
     # native exchange engine (engine.cu)
     "gmt_engine_default_device": (None, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "gmt_engine2d_create": (None, [C.c_int, C.c_int, C.POINTER(C.c_int), c_i64, c_i64, C.c_int, C.c_int, C.c_int,
@@ -152,6 +158,8 @@ _SIGS = {
     "gmt_engine2d_array": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(c_ptr), C.POINTER(c_i64), C.POINTER(c_i64)]),
     "gmt_engine2d_init_analytic": (None, [c_ptr, C.c_double]),
     "gmt_engine2d_step": (None, [c_ptr]),
+    "gmt_engine2d_exchange": (None, [c_ptr]),
+    "gmt_engine2d_time_exchanges": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "gmt_engine2d_synchronize": (None, [c_ptr]),
     "gmt_engine2d_status": (None, [c_ptr, C.POINTER(C.c_int)]),
     "gmt_engine2d_time_steps": (None, [c_ptr, C.c_int, C.c_int, C.POINTER(C.c_double)]),
@@ -190,13 +198,14 @@ class _Lib:
 
     def load(self):
         if self._dll is None:
-            if not LIB_PATH.exists():
-                # build outputs are git-ignored: a fresh checkout compiles them on first use (one process builds,
-                # the other ranks wait on a file lock); no compiler -> a loud error, never a fallback
-                try:
-                    from .._native.build import ensure_built
-                    ensure_built()
-                except Exception as exc:  # noqa: BLE001
+            # build outputs are git-ignored: a fresh checkout compiles them on first use, an edited tree
+            # recompiles what is stale (one process builds, the other ranks wait on a file lock);
+            # no library and no compiler -> a loud error, never a fallback
+            try:
+                from .._native.build import ensure_built
+                ensure_built()
+            except Exception as exc:  # noqa: BLE001
+                if not LIB_PATH.exists():
                     raise GmtError("load", -1, f"{LIB_PATH} not found and building it failed ({exc}); run "
                                    "`python -m gpu_mpi_tests_b200._native.build` (or __graft_entry__.build())") from exc
             self._dll = C.CDLL(str(LIB_PATH), mode=C.RTLD_GLOBAL)

@@ -30,15 +30,17 @@ def _dev_ptr_array(ptrs, device) -> torch.Tensor:
 
 
 class PeerCollectives:
-    def __init__(self, space: PeerSpace, buf_doubles: int = 0, stage_cap: int = 4096, spin_limit: int = 0):
+    def __init__(self, space: PeerSpace, buf_doubles: int = 0, stage_cap: int = 8192, spin_limit: int = 0):
         if space.world > MAX_WORLD:
             raise ValueError(f"world {space.world} > {MAX_WORLD}")
         self.space, self.device = space, space.device
         self.world, self.ranks = space.world, list(space.ranks_here)
-        self.buf_doubles, self.stage_cap = int(buf_doubles), max(int(stage_cap), 8)
+        # at least gmt_coll_min_stage_cap() cells per source rank: daxpy + global sum stores one per CTA
+        self.buf_doubles, self.stage_cap = int(buf_doubles), max(int(stage_cap), int(lib.gmt_coll_min_stage_cap()))
         self.spin_limit = int(spin_limit)
+        self.ll_gather_max = min(self.stage_cap, int(lib.gmt_coll_ll_gather_max()))
         self._buf = space.alloc(max(self.buf_doubles, 4) * 8)
-        self._stage = space.alloc((4 + 4 * space.world) * self.stage_cap * 8)   # vectors + LL cells, zeroed
+        self._stage = space.alloc(int(lib.gmt_coll_stage_bytes(space.world, self.stage_cap)))   # vectors + LL cells, zeroed
         self._flags = space.alloc(FLAG_WORDS * 8)
         n = len(self.ranks)
         self._epoch = torch.zeros(n, 8, dtype=torch.int64, device=self.device)
@@ -95,6 +97,8 @@ class PeerCollectives:
 
     def check_status(self) -> None:
         st = self._status[:, 0].tolist()
+        if any(v & 0x1000 for v in st):
+            raise CollectiveTimeout(f"a collective needed more LL cells than stage_cap={self.stage_cap}: status {st}")
         if any(st):
             raise CollectiveTimeout(f"collective wait expired: status per hosted rank {st} (1 + silent rank)")
 
@@ -102,19 +106,37 @@ class PeerCollectives:
         return self._epoch[:, 0].tolist()
 
     # ------------------------------------------------------------------ collectives
-    def allgather_inplace(self, n: int, multicast: bool = False) -> None:
+    GATHER_MODES = {"p2p": 0, "multimem": 1, "ll": 2, "multimem_weak": 3, "mc_store": 4}
+
+    def _gather_mode(self, n: int, multicast, mode: str | None) -> int:
+        """mode: "p2p" (world-1 peer stores per 32 bytes), "ll" (epoch-carrying cells, slices up to
+        64 KiB: one one-way trip, no signalling rounds), "multimem" / "multimem_weak" / "mc_store"
+        (NVLS: the switch replicates one store); None = ll when the slice fits, else p2p."""
+        if mode is None:
+            if multicast:
+                mode = "multimem"
+            else:
+                mode = "ll" if (self.world > 1 and n <= self.ll_gather_max) else "p2p"
+        m = self.GATHER_MODES[mode]
+        if m in (1, 3, 4) and not self.has_multicast:
+            m = 0
+        if m == 2 and n > self.ll_gather_max:
+            raise ValueError(f"LL allgather takes slices of up to {self.ll_gather_max} doubles, got {n}")
+        return m
+
+    def allgather_inplace(self, n: int, multicast: bool = False, mode: str | None = None) -> None:
         """Every rank's slot [r*n, (r+1)*n) of buffer(r) ends up in every rank's buffer."""
         self._check_gather(n)
         self.bind({})
         lib.gmt_allgather_f64(self._ranks_dev.data_ptr(), len(self.ranks), n, 0,
-                              int(multicast and self.has_multicast), self._stream())
+                              self._gather_mode(n, multicast, mode), self._stream())
 
-    def allgather(self, n: int, src: dict, multicast: bool = False) -> None:
+    def allgather(self, n: int, src: dict, multicast: bool = False, mode: str | None = None) -> None:
         """Out-of-place source: slot r of every buffer <- src[r] (n doubles)."""
         self._check_gather(n)
         self.bind({r: (src[r], None, None) for r in self.ranks})
         lib.gmt_allgather_f64(self._ranks_dev.data_ptr(), len(self.ranks), n, 1,
-                              int(multicast and self.has_multicast), self._stream())
+                              self._gather_mode(n, multicast, mode), self._stream())
 
     def gather_inplace(self, n: int, root: int = 0) -> None:
         self._check_gather(n)
@@ -149,6 +171,8 @@ class PeerCollectives:
     def daxpy_allreduce(self, a: float, x: dict, y: dict, out: dict) -> None:
         """y[r] <- a*x[r] + y[r]; out[r][0] <- sum over all ranks of sum(y_new)."""
         n = next(iter(x.values())).numel()
+        if any(x[r].numel() != n or y[r].numel() != n for r in self.ranks):
+            raise ValueError("daxpy_allreduce: every rank must pass the same n")
         self.bind({r: (x[r], out[r], y[r]) for r in self.ranks})
         lib.gmt_daxpy_allreduce_f64(self._ranks_dev.data_ptr(), len(self.ranks), n, float(a), self._stream())
 

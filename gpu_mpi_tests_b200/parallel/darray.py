@@ -11,10 +11,14 @@ methods:
     a.exchange()                                     # ghost cells <- neighbours (library path)
     d = a.derivative()                               # exchange fused into the stencil kernel
 
-`exchange()` is the library (NCCL/gloo) halo exchange of baseline/exchange.py and works on
-CPUs; `derivative()` uses the fused peer-memory kernel on GPUs (the exchange happens inside
-it and also leaves the ghost cells filled) and exchange()+stencil on CPUs.  Arrays follow the
-reference's column-major convention: `local` has torch shape (n_dim1 [+4], n_dim0 [+4]).
+`exchange()` fills the ghost cells and nothing else: on GPUs it is the peer-memory exchange kernel
+(gmt_halo_exchange1d/2d_f64: boundary values stored straight into the neighbours' inboxes, flags,
+landing -- no pack buffers, no library call), so ANY compute step of the user's can follow it; on
+CPUs it is the library (gloo) exchange of baseline/exchange.py.  `derivative()` uses the fused
+kernel on GPUs (the exchange happens inside the sweep and also leaves the ghost cells filled) and
+exchange()+stencil on CPUs.  `apply(fn)` runs a user function on the exchanged local array.
+Arrays follow the reference's column-major convention: `local` has torch shape
+(n_dim1 [+4], n_dim0 [+4]).
 """
 from __future__ import annotations
 
@@ -56,12 +60,13 @@ class DistArray1D:
         self._wl.setup()
 
     def exchange(self) -> None:
-        """Fill the ghost cells from the neighbours (library path; on the fused path a full
-        derivative step does it as a side effect, so that is what runs)."""
-        if self.impl == "baseline":
-            self._wl.exchange_only()
-        else:
-            self._wl.step()
+        """Fill the ghost cells from the neighbours; the interior and the result are untouched."""
+        self._wl.exchange_only()
+
+    def apply(self, fn):
+        """exchange(), then fn(local ghosted array) -- the hook for a user's own compute step."""
+        self.exchange()
+        return fn(self.local)
 
     def derivative(self) -> torch.Tensor:
         """dy/dx with the 5-point stencil, ghosts refreshed on the way."""
@@ -107,10 +112,14 @@ class DistArray2D:
         self._wl.setup(poison=poison)
 
     def exchange(self) -> None:
-        if self.impl == "baseline":
-            self._wl.plan.exchange()
-        else:
-            self._wl.step()
+        """Fill the ghost cells of every decomposed side from the neighbours; the interior and the
+        result array are untouched."""
+        self._wl.exchange()
+
+    def apply(self, fn):
+        """exchange(), then fn(local ghosted array) -- the hook for a user's own compute step."""
+        self.exchange()
+        return fn(self.local)
 
     def derivative(self) -> torch.Tensor:
         """d/dx (dims has 0) + d/dy (dims has 1), ghosts refreshed on the way."""

@@ -69,10 +69,15 @@ def best_grid(world: int) -> tuple[int, int]:
 @dataclass(frozen=True)
 class Grid2D:
     """px x py process grid; rank = cx + cy*px.  Side order matches the kernels:
-    0 = low x, 1 = high x, 2 = low y, 3 = high y."""
+    0 = low x, 1 = high x, 2 = low y, 3 = high y.
+
+    periodic=True wraps both directions (an extension: the reference's exchanges never wrap,
+    mpi_stencil_gt.cc:94-107), so that EVERY rank has four live faces whatever the grid shape --
+    with one rank along a direction the rank is its own neighbour there."""
     px: int
     py: int
     rank: int
+    periodic: bool = False
 
     def __post_init__(self):
         if not (0 <= self.rank < self.px * self.py):
@@ -102,6 +107,8 @@ class Grid2D:
             cy += 1
         else:
             raise ValueError("side must be 0..3")
+        if self.periodic:
+            return (cx % self.px) + (cy % self.py) * self.px
         if 0 <= cx < self.px and 0 <= cy < self.py:
             return cx + cy * self.px
         return -1

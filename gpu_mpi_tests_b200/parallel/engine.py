@@ -73,6 +73,16 @@ class NativeEngine2D:
     def step(self) -> None:
         lib.gmt_engine2d_step(self._h)
 
+    def exchange(self) -> None:
+        """The halo exchange alone (no sweep); can be mixed with step()."""
+        lib.gmt_engine2d_exchange(self._h)
+
+    def time_exchanges(self, steps: int, warmup: int = 5) -> float:
+        """ms per exchange-only call, device time, max over the GPUs."""
+        ms = C.c_double()
+        lib.gmt_engine2d_time_exchanges(self._h, steps, warmup, C.byref(ms))
+        return ms.value
+
     def synchronize(self) -> None:
         lib.gmt_engine2d_synchronize(self._h)
 

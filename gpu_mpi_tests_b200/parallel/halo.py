@@ -121,6 +121,14 @@ class FusedStencil1D(_PlanBase):
                                     torch.cuda.current_stream().cuda_stream)
         self.steps += 1
 
+    def exchange(self) -> None:
+        """The halo exchange alone (boundary_exchange, mpi_stencil_gt.cc:83-122): afterwards z's
+        ghost cells hold the neighbours' boundary values; `out` is untouched.  One small kernel
+        per rank over the same peer inboxes / flags / epoch as step(); the two can be mixed."""
+        lib.gmt_halo_exchange1d_f64(self._ranks_dev.data_ptr(), len(self.ranks),
+                                    torch.cuda.current_stream().cuda_stream)
+        self.steps += 1
+
 
 class FusedStencil2D(_PlanBase):
     """2-D array z = x^3 + y^2 on a px x py process grid with ghosts of width gx, gy and the
@@ -129,22 +137,32 @@ class FusedStencil2D(_PlanBase):
     gx=2, gy=0 on a (world x 1) grid is the reference's dim-0 test, gx=0, gy=2 on (1 x world)
     its dim-1 test (mpi_stencil2d_gt.cc:385-572); gx=gy=2 is the 4-neighbour case of BASELINE
     config 3.  nx, ny are per-rank interior extents (weak scaling, mpi_stencil2d_gt.cc:395).
+    periodic=True wraps the process grid, so every rank exchanges all of its used faces (an
+    8-GPU 4 x 2 grid then has four live faces on every rank; without it at most three).
     """
 
     def __init__(self, space: PeerSpace, px: int, py: int, nx: int, ny: int, gx: int = 2, gy: int = 2,
                  with_err: bool = True, spin_limit: int = 0, dx: float | None = None, dy: float | None = None,
-                 wx: float = 1.0, wy: float = 1.0, mem_space: str = "device", host_fed: bool = False):
+                 wx: float = 1.0, wy: float = 1.0, mem_space: str = "device", host_fed: bool = False,
+                 periodic: bool = False):
         super().__init__(space, with_err, spin_limit)
+        if periodic and with_err:
+            raise ValueError("periodic grids have no analytic error norm (x^3 + y^2 does not wrap): with_err=False")
         if px * py != space.world:
             raise ValueError(f"grid {px}x{py} does not match world {space.world}")
         if nx % 4:
             raise ValueError("fused 2-D exchange needs nx % 4 == 0 (256-bit rows)")
         self.px, self.py, self.nx, self.ny, self.gx, self.gy = px, py, nx, ny, gx, gy
-        self.dx = dx if dx is not None else DOMAIN_LENGTH / (nx * px)
-        self.dy = dy if dy is not None else DOMAIN_LENGTH / (ny * py)
+        # slab decompositions (one differentiated dim) are the reference's tests: ONE spacing,
+        # 8 / n_global_deriv, for both coordinates (mpi_stencil2d_gt.cc:427-448)
+        dflt_x = DOMAIN_LENGTH / (nx * px) if (gx or not gy) else DOMAIN_LENGTH / (ny * py)
+        dflt_y = DOMAIN_LENGTH / (ny * py) if (gy or not gx) else DOMAIN_LENGTH / (nx * px)
+        self.dx = dx if dx is not None else dflt_x
+        self.dy = dy if dy is not None else dflt_y
         self.sx = wx / self.dx if gx else 0.0
         self.sy = wy / self.dy if gy else 0.0
-        self.grids = {r: Grid2D(px, py, r) for r in self.ranks}
+        self.periodic = bool(periodic)
+        self.grids = {r: Grid2D(px, py, r, self.periodic) for r in self.ranks}
         self.ldz = nx + 2 * gx
         # only inboxes and flags are touched by peers; the arrays themselves may live in any
         # memory space the GPU can address (device, or managed for the TEST_MANAGED flavours)
@@ -185,7 +203,9 @@ class FusedStencil2D(_PlanBase):
             if fed:
                 self.hostbox[r] = torch.zeros(total, dtype=F64, device=self.device)
                 self._hostflags[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, device=self.device)
-                self._hostflags_pinned[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, pin_memory=True)
+                # two pinned sources: a pipelined caller enqueues step s+1 before step s has run
+                self._hostflags_pinned[r] = [torch.zeros(4, max(nfx, nfy), dtype=torch.int64, pin_memory=True)
+                                             for _ in range(2)]
             off = 0
             for side in range(4):
                 used = gx if side < 2 else gy
@@ -245,6 +265,15 @@ class FusedStencil2D(_PlanBase):
                                     int(self.with_err), torch.cuda.current_stream().cuda_stream)
         self.steps += 1
 
+    def exchange(self) -> None:
+        """The halo exchange alone (boundary_exchange_x / _y, mpi_stencil2d_gt.cc:136-373): afterwards
+        z's ghost cells of every side with a neighbour hold that neighbour's boundary rows / columns;
+        `out` is untouched, so any compute step of the caller's can follow.  One small kernel per
+        rank over the same peer inboxes / flags / epoch as step(); the two can be mixed."""
+        lib.gmt_halo_exchange2d_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.nx, self.ny, self.gx, self.gy,
+                                    torch.cuda.current_stream().cuda_stream)
+        self.steps += 1
+
     # ---- host-fed sides ------------------------------------------------------------------
     def host_side_shape(self, side: int) -> tuple:
         """Shape of the host tensor feeding `side`: x faces (ny, 2) [2 ghost rows per column],
@@ -257,20 +286,21 @@ class FusedStencil2D(_PlanBase):
         return [z[gy:gy + ny, 0:2], z[gy:gy + ny, gx + nx:gx + nx + 2], z[0:2, gx:gx + nx],
                 z[gy + ny:gy + ny + 2, gx:gx + nx]][side]
 
-    def publish_host_sides_by_copy(self, rank: int) -> None:
+    def publish_host_sides_by_copy(self, rank: int, slot: int = 0) -> None:
         """Publish the host-fed sides' flags for the NEXT step with a host-to-device copy on the
         current stream (enqueue it right after the copy of the values).  A copy engine needs no SM,
         so this cannot be starved by the very kernel that is waiting for it -- a publishing kernel
-        could be, once the fused kernel's CTAs occupy every SM.  The pinned source holds the epoch
-        of the next step; it is rewritten by the host before every step."""
+        could be, once the fused kernel's CTAs occupy every SM.  The pinned source `slot` holds the
+        epoch of the next step; it is rewritten by the host before every step (a pipelined caller
+        alternates the two slots, so the source of a step still in the queue is never rewritten)."""
         if rank in self._hostflags:
-            self._hostflags_pinned[rank].fill_(self.steps + 1)
-            self._hostflags[rank].copy_(self._hostflags_pinned[rank], non_blocking=True)
+            self._hostflags_pinned[rank][slot].fill_(self.steps + 1)
+            self._hostflags[rank].copy_(self._hostflags_pinned[rank][slot], non_blocking=True)
 
-    def refresh_host_epoch(self) -> None:
-        """Before replaying a captured step: put the next epoch into the pinned flag sources."""
+    def refresh_host_epoch(self, slot: int = 0) -> None:
+        """Before replaying a captured step: put the next epoch into the pinned flag source `slot`."""
         for rank in self._hostflags_pinned:
-            self._hostflags_pinned[rank].fill_(self.steps + 1)
+            self._hostflags_pinned[rank][slot].fill_(self.steps + 1)
 
     def publish_host_sides(self, rank: int) -> None:
         """Kernel flavour, for use on the SAME stream BEFORE the fused kernel (plain step() of a

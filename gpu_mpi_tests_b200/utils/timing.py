@@ -57,16 +57,22 @@ def _barrier(device: torch.device) -> None:
             dist.barrier()
 
 
-def time_steps(step_fn, steps: int, warmup: int, device: torch.device) -> dict:
+def time_steps(step_fn, steps: int, warmup: int, device: torch.device, tail=None) -> dict:
     """`warmup` untimed calls, then exactly `steps` calls timed on the device, bracketed by a
-    barrier + synchronize on both sides; returns total/mean ms as the max over ranks."""
+    barrier + synchronize on both sides; returns total/mean ms as the max over ranks.  `tail`,
+    when given, runs inside the timed region after the last call (e.g. the flush of a pipelined
+    loop, so that every result has been read back before the clock stops)."""
     for _ in range(warmup):
         step_fn()
+    if tail is not None:
+        tail()
     if device.type != "cuda":
         _barrier(device)
         t0 = time.perf_counter()
         for _ in range(steps):
             step_fn()
+        if tail is not None:
+            tail()
         _barrier(device)
         ms = (time.perf_counter() - t0) * 1e3
         ms = max_over_ranks(ms, device)
@@ -78,6 +84,8 @@ def time_steps(step_fn, steps: int, warmup: int, device: torch.device) -> dict:
     e0.record()
     for _ in range(steps):
         step_fn()
+    if tail is not None:
+        tail()
     e1.record()
     torch.cuda.synchronize(device)
     ms = e0.elapsed_time(e1)
@@ -85,6 +93,36 @@ def time_steps(step_fn, steps: int, warmup: int, device: torch.device) -> dict:
     torch.cuda.synchronize(device)
     ms = max_over_ranks(ms, device)
     return {"total_ms": ms, "ms_per_step": ms / max(steps, 1)}
+
+
+def time_graph(step_fn, iters: int, warmup: int, device: torch.device) -> tuple[float, str]:
+    """Per-call ms of a launch-bound op: `iters` calls captured in ONE CUDA graph and replayed, so the
+    Python/driver launch cost is out of the measurement for the peer-memory kernels and the library
+    calls alike (device-timed, max over ranks).  Falls back to eager event timing when the op cannot
+    be captured; the second value says which ("graph" / "eager")."""
+    try:
+        for _ in range(warmup):
+            step_fn()
+        torch.cuda.synchronize(device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(iters):
+                step_fn()
+        g.replay()
+        torch.cuda.synchronize(device)
+        _barrier(device)
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize(device)
+        ms = e0.elapsed_time(e1) / iters
+        del g
+        return max_over_ranks(ms, device), "graph"
+    except Exception:  # noqa: BLE001
+        torch.cuda.synchronize(device)
+        return time_steps(step_fn, iters, warmup, device)["ms_per_step"], "eager"
 
 
 def time_each(step_fn, iters: int, warmup: int, device: torch.device) -> list:

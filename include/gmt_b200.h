@@ -110,11 +110,14 @@ int gmt_daxpy_sum_f64(int64_t n, double a, const double* x, double* y, double* o
  *   - n is limited to gmt_noalloc_max_n() = 33,554,432 elements (one partial per
  *     4096-element chunk must fit the array); larger n returns GMT_ETOOBIG.
  *   - The first call on each device looks up the array's device address; make that first
- *     call before any stream capture.
+ *     call before any stream capture (a first call on a capturing stream returns
+ *     GMT_EUNSUPPORTED).  The address is kept for the life of the process: do not call
+ *     cudaDeviceReset() between calls.
  *   - All calls on a device share the array, which keeps the previous call's contents; the
  *     counter that must start at zero is cleared on `stream` by every call.  Calls that overlap
  *     on the GPU (unordered streams, concurrent host threads) race on it: order them.
- *   - The partials are added in index order: the sum is bit-reproducible run to run.        */
+ *   - The partials are added in a fixed order (strided over the threads of the last block, then
+ *     a shuffle tree): the sum is bit-reproducible run to run, though not a left-to-right sum. */
 int gmt_daxpy_sum_noalloc_f64(int64_t n, double a, const double* x, double* y, double* out_sum,
                               gmt_stream_t stream);
 int64_t gmt_noalloc_max_n(void);
@@ -227,6 +230,12 @@ typedef struct {
 /* replaces boundary_exchange + stencil1d_5 (mpi_stencil_gt.cc:83-122,206) */
 int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, int with_err,
                             gmt_stream_t stream);
+/* The exchange alone -- boundary_exchange as a callable (mpi_stencil_gt.cc:83-122) and the
+ * quantity the reference times (:200-204): store my two boundary values into each neighbour's
+ * inbox, wait for theirs, put them into z's ghost cells.  Same descriptors, inboxes, flags and
+ * epoch as gmt_fused_stencil1d_f64 (calls of both kinds can be mixed; each advances the epoch);
+ * `out` and the error fields are not touched.  One 64-thread CTA per rank. */
+int gmt_halo_exchange1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, gmt_stream_t stream);
 
 /* 2-D: sides 0 = low x (dim 0), 1 = high x, 2 = low y (dim 1), 3 = high y.
  * gx, gy in {0, 2} are the ghost widths of z in each dim; z is (nx+2gx, ny+2gy) and
@@ -261,6 +270,15 @@ typedef struct {
 
 int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
                             int gx, int gy, int with_err, gmt_stream_t stream);
+/* The exchange alone -- boundary_exchange_x / _y as a callable (mpi_stencil2d_gt.cc:136-373) and
+ * the quantity the reference times (:512-522): every used side's two boundary rows / columns go
+ * into the neighbour's inbox (strided 16-byte pieces gathered into contiguous peer stores for the
+ * x faces, contiguous for the y faces), chunk flags follow, and what the neighbours (or the host,
+ * has == 2) delivered is put into z's own ghost cells.  No sweep: afterwards z is what it is after
+ * the reference's exchange, for any compute step of the caller's.  Same descriptors and epoch as
+ * gmt_fused_stencil2d_f64; calls of both kinds can be mixed on one plan. */
+int gmt_halo_exchange2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
+                            int gx, int gy, gmt_stream_t stream);
 /* For sides with has == 2: after the host-to-device copy of the ghost values into my_inbox, publish
  * "arrived" for the step that is currently running / about to run: flags[i] <- *epoch + 1 (release).
  * Call it on the stream that carried the copy; it may run concurrently with that step's kernel. */
@@ -268,6 +286,10 @@ int gmt_publish_epoch_flags(uint64_t* flags, int64_t n, const uint64_t* epoch, g
 /* Test hook: sleep a pseudo-random time of up to max_ns nanoseconds before every halo flag
  * store (0 = off, the default).  Shakes the flag/epoch/parity protocol in stress tests.   */
 int gmt_debug_set_push_delay(unsigned int max_ns);
+/* Test hook: `ctas` thread blocks of 1024 threads (two fill an SM) that hold their SM slots for
+ * `ns` nanoseconds and do nothing else -- for tests that a kernel of this library does not depend on
+ * having the whole GPU (no counterpart in the reference). */
+int gmt_debug_occupy(int ctas, unsigned long long ns, gmt_stream_t stream);
 /* flag words needed on `side` for the given interior extents */
 int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
 
@@ -278,9 +300,21 @@ int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
  *
  * Signalling: every rank owns a flag block of GMT_COLL_FLAG_WORDS words; word [round*32 + src]
  * (rounds 0,1) holds the last epoch rank `src` signalled for that round (st.release.sys /
- * ld.acquire.sys, bounded spins); words [64 + (parity*32 + src)*2 ..] are "LL" slots in which a
- * scalar travels as two 8-byte words that each carry 32 payload bits and the 32-bit epoch.  Epochs only grow; reduction inputs travel through a staging area that is
- * double-buffered by epoch parity, so a rank that is one call ahead cannot disturb a slower one. */
+ * ld.acquire.sys, bounded spins).  Epochs only grow; reduction inputs travel through a staging
+ * area that is double-buffered by epoch parity, so a rank that is one call ahead cannot disturb a
+ * slower one.  Small payloads skip the flags altogether: they travel as 16-byte "LL" cells in the
+ * staging area whose two 8-byte words each carry 32 payload bits and the 32-bit epoch, so data and
+ * "arrived" come in one store (LL all-reduce, allgather of slices up to 64 KiB, and the per-CTA
+ * partial sums of gmt_daxpy_allreduce_f64).
+ *
+ * Sizes: a staging area is gmt_coll_stage_bytes(world, stage_cap) bytes; stage_cap must be at least
+ * gmt_coll_min_stage_cap() (= 2048: gmt_daxpy_allreduce_f64 stores one cell per CTA, up to 2048).
+ * The raw entry points cannot see stage_cap from the host; a kernel that would need more cells
+ * than the descriptor's stage_cap writes nothing, sets bit 0x1000 in the status word and (daxpy)
+ * returns NaN.  The engines and the Python layer check sizes on the host and return GMT_ETOOBIG. */
+size_t gmt_coll_stage_bytes(int world, int64_t stage_cap);
+int64_t gmt_coll_min_stage_cap(void);
+int64_t gmt_coll_ll_gather_max(void);   /* largest slice (doubles) gmt_allgather_f64 takes in LL mode */
 #define GMT_COLL_FLAG_WORDS 256
 #define GMT_COLL_MAX_WORLD 32
 typedef struct {
@@ -288,15 +322,16 @@ typedef struct {
   double** peer_buf;      /* device array [world]: each rank's symmetric USER buffer (allgather/gather) */
   double* mc_buf;         /* NVLS multicast address of that buffer, or NULL */
   double** peer_stage;    /* device array [world]: each rank's ZERO-INITIALISED staging area of
-                             (4 + 4*world)*stage_cap doubles: inputs [parity][stage_cap], results
-                             [parity][stage_cap], then the "LL" cells [parity][src rank][stage_cap] of 16 bytes */
+                             gmt_coll_stage_bytes(world, stage_cap) = (4 + 4*world)*stage_cap doubles: inputs
+                             [parity][stage_cap], results [parity][stage_cap], then the "LL" cells
+                             [parity][src rank][stage_cap] of 16 bytes */
   double* mc_stage;       /* multicast address of the staging area, or NULL */
   int64_t stage_cap;
   uint64_t** peer_flag;   /* device array [world]: each rank's flag block */
   uint64_t* epoch;        /* device-resident epoch counter of this rank */
   uint32_t* done;         /* >= 4 zero-initialised words (self-resetting) */
-  uint32_t* status;       /* non-zero when a bounded spin expired */
-  void* scratch;          /* gmt_reduce_scratch_bytes() of zeroed local scratch */
+  uint32_t* status;       /* 1 + silent rank when a bounded spin expired; bit 0x1000: stage_cap too small for the call */
+  void* scratch;          /* gmt_reduce_scratch_bytes() of zeroed local scratch (unused since the LL-cell daxpy) */
   const double* in;       /* local operand: allgather source / all-reduce input / axis-sum array / daxpy x */
   double* out;            /* local result: all-reduce output vector / global sum */
   double* y;              /* daxpy y */
@@ -307,7 +342,12 @@ typedef struct {
  * peer's buffer (MPI_Allgather(MPI_IN_PLACE), mpi_daxpy_nvtx.cc:285, mpigatherinplace.f90:39).
  * from_in != 0: the slice is read from `in` instead of the rank's own slot, and also stored
  * locally (MPI_Allgather with a separate send buffer, mpi_daxpy_nvtx.cc:288).
- * use_multicast != 0: one multimem.st per 16 bytes through mc_buf instead of world-1 stores. */
+ * use_multicast (a mode): 0 = world-1 peer stores per 32 bytes; 1 = multimem.st.relaxed.sys through
+ * mc_buf (one store per 16 bytes, the switch replicates); 3 = the same with weak multimem.st;
+ * 4 = ordinary 256-bit stores on the multicast mapping; 2 = "LL": slices of up to
+ * gmt_coll_ll_gather_max() doubles (and <= stage_cap) travel as epoch-carrying 16-byte cells through
+ * the staging area and every rank copies them into its own buffer -- one one-way trip, no
+ * signalling rounds, nobody writes anybody else's user buffer. */
 int gmt_allgather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int from_in,
                       int use_multicast, gmt_stream_t stream);
 /* gather to root in place (MPI_Gather with MPI_IN_PLACE at the root, BASELINE config 5).  Ends with an
@@ -324,11 +364,18 @@ int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int r
  * Ranks add in rank order, so every rank gets the same bits (algos 0, 1 and 3).          */
 int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int algo, gmt_stream_t stream);
 /* fused daxpy + global sum: y <- a*in + y on each rank, every rank's *out <- sum over all ranks
- * of sum(y_new)  (cublasDaxpy + MPI_Allgather + host sums, mpi_daxpy_nvtx.cc:245-310, in one kernel) */
+ * of sum(y_new)  (cublasDaxpy + MPI_Allgather + host sums, mpi_daxpy_nvtx.cc:245-310, in one kernel).
+ * One-shot grid in address order; every CTA stores its partial as an LL cell into every rank's
+ * staging area and the last CTA of each rank adds all world x grid cells in a fixed order (same
+ * bits on every rank, reproducible).  Needs stage_cap >= gmt_coll_min_stage_cap(); n must be the
+ * same on every rank. */
 int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, double a,
                             gmt_stream_t stream);
 /* axis sum of the column-major (nx, ny, ld) array `in` whose epilogue all-reduces the first n_out
- * entries across ranks into `out` (gt::sum_axis_to + MPI_Allreduce, mpi_stencil2d_gt.cc:611-625) */
+ * entries across ranks into `out` (gt::sum_axis_to + MPI_Allreduce, mpi_stencil2d_gt.cc:611-625).
+ * n_out <= stage_cap.  LL cells while n_out x world <= 2^18, one-shot beyond (chosen in the kernel,
+ * which knows the world size).  Safe without co-residency of its grid: whoever waits for a cell
+ * waits for another rank only. */
 int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
                                int64_t ld, int axis, int64_t n_out, gmt_stream_t stream);
 /* signal barrier across ranks (MPI_Barrier, mpi_daxpy_nvtx.cc:277) */
@@ -345,7 +392,9 @@ int gmt_barrier(const gmt_coll_rank* ranks_dev, int n_ranks, gmt_stream_t stream
  * access; ranks sharing a GPU go into one cooperative launch.  Everything is allocated in
  * create(); step() only launches (one fused halo+stencil kernel per GPU, asynchronous).
  * Per-rank interior is nx x ny (weak scaling), domain [0,8) per decomposed direction,
- * z = x^3 + y^2, out = d/dx (gx == 2) + d/dy (gy == 2).  Not thread-safe per engine.    */
+ * z = x^3 + y^2, out = d/dx (gx == 2) + d/dy (gy == 2).  Slab decompositions (only one of gx, gy)
+ * use ONE spacing, 8 / n_global of the differentiated axis, for both coordinates, like the
+ * reference's test_deriv (mpi_stencil2d_gt.cc:427-448).  Not thread-safe per engine.    */
 typedef struct gmt_engine2d gmt_engine2d;
 int gmt_engine_default_device(int n_ranks, int rank, int n_devices, int* device);
 int gmt_engine2d_create(int px, int py, const int* devices, int64_t nx, int64_t ny, int gx, int gy,
@@ -359,18 +408,23 @@ int gmt_engine2d_array(const gmt_engine2d* e, int rank, int which, double** ptr,
 /* analytic field; ghosts analytic on physical sides, `poison` on sides a neighbour must fill */
 int gmt_engine2d_init_analytic(gmt_engine2d* e, double poison);
 int gmt_engine2d_step(gmt_engine2d* e);          /* asynchronous */
+/* the halo exchange alone (gmt_halo_exchange2d_f64 on every GPU), asynchronous; can be mixed with step() */
+int gmt_engine2d_exchange(gmt_engine2d* e);
 int gmt_engine2d_synchronize(gmt_engine2d* e);
 /* GMT_ETIMEOUT (and the rank) when some rank's bounded flag wait expired */
 int gmt_engine2d_status(gmt_engine2d* e, int* first_bad_rank);
 /* warm-up, then `steps` steps bracketed by CUDA events on every GPU's stream; max over GPUs */
 int gmt_engine2d_time_steps(gmt_engine2d* e, int steps, int warmup, double* ms_per_step);
+/* the same for exchange-only calls: the reference's timed quantity (mpi_stencil2d_gt.cc:512-522) */
+int gmt_engine2d_time_exchanges(gmt_engine2d* e, int steps, int warmup, double* ms_per_exchange);
 /* sqrt of the in-kernel sum((out - analytic)^2) of the last step (needs with_err) */
 int gmt_engine2d_err_norm(gmt_engine2d* e, int rank, double* err_norm);
 
 /* Collective engine (engine_coll.cu): the same single-process arrangement for the collectives --
  * the host side of the reference's daxpy benchmark and gather test (mpi_daxpy_nvtx.cc:85-343,
  * mpigatherinplace.f90:1-58).  Every rank owns a symmetric user buffer of buf_doubles doubles
- * (gathered arrays live there) and a staging area of 4*stage_cap doubles; each call below is one
+ * (gathered arrays live there) and a staging area of gmt_coll_stage_bytes(world, stage_cap) bytes
+ * (stage_cap is raised to gmt_coll_min_stage_cap() if smaller); each call below is one
  * asynchronous launch per GPU on the engine's per-GPU stream (gmt_coll_engine_stream: order your
  * own work on a rank's operands on that stream).  No NVLS multicast variants here.            */
 typedef struct gmt_coll_engine gmt_coll_engine;

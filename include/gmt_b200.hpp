@@ -101,12 +101,19 @@ class Engine2D {
   int device_groups() const { return gmt_engine2d_device_groups(e_); }
   void init_analytic(double poison = 0.0) { check(gmt_engine2d_init_analytic(e_, poison), "init_analytic"); }
   void step() { check(gmt_engine2d_step(e_), "step"); }
+  void exchange() { check(gmt_engine2d_exchange(e_), "exchange"); }
   void synchronize() { check(gmt_engine2d_synchronize(e_), "synchronize"); }
   void status() { check(gmt_engine2d_status(e_, nullptr), "status"); }
   double time_steps(int steps, int warmup)
   {
     double ms = 0.0;
     check(gmt_engine2d_time_steps(e_, steps, warmup, &ms), "time_steps");
+    return ms;
+  }
+  double time_exchanges(int steps, int warmup)
+  {
+    double ms = 0.0;
+    check(gmt_engine2d_time_exchanges(e_, steps, warmup, &ms), "time_exchanges");
     return ms;
   }
   double err_norm(int rank)

@@ -49,10 +49,14 @@ static int run_case(const Case& c, int n_iter, int n_warmup)
     if ((rc = gmt_engine2d_err_norm(eng, r, &err)) != 0) return die("gmt_engine2d_err_norm", rc);
     err_sum += err;
   }
+  // the reference's own timed quantity: the exchange alone (mpi_stencil2d_gt.cc:512-522)
+  double ex_ms = 0.0;
+  if ((rc = gmt_engine2d_time_exchanges(eng, n_iter < 20 ? n_iter : 20, 3, &ex_ms)) != 0)
+    return die("gmt_engine2d_time_exchanges", rc);
   const double glups = double(c.nx) * double(c.ny) * world / (ms * 1e-3) / 1e9;
   std::printf("TEST %s, device , fused; %0.8f, err=%0.8f\n", c.label, ms * 1e-3 * n_iter, err_sum);
-  std::printf("     %d ranks on %d GPU(s), %lld x %lld per rank: %0.4f ms/step, %0.1f GLUP/s\n", world,
-              gmt_engine2d_device_groups(eng), c.nx, c.ny, ms, glups);
+  std::printf("     %d ranks on %d GPU(s), %lld x %lld per rank: %0.4f ms/step, %0.1f GLUP/s; exchange alone %0.2f us\n",
+              world, gmt_engine2d_device_groups(eng), c.nx, c.ny, ms, glups, ex_ms * 1e3);
   gmt_engine2d_destroy(eng);
   return 0;
 }

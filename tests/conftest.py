@@ -27,9 +27,8 @@ def pytest_collection_modifyitems(config, items):
 def native():
     """The native library, built in-tree; GPU tests must never run on a silent fallback."""
     from gpu_mpi_tests_b200.ops import _lib
-    if not _lib.have_native():
-        from gpu_mpi_tests_b200._native.build import build
-        build()
+    from gpu_mpi_tests_b200._native.build import ensure_built
+    ensure_built()     # also rebuilds after an edit of csrc/ or include/: never test a stale library
     _lib.require_native()
     return _lib.lib
 

@@ -261,6 +261,31 @@ def test_dist_arrays_world_of_one_cpu(monkeypatch):
     runtime.finalize()
 
 
+@pytest.mark.parametrize("dim", [0, 1])
+def test_slab_modes_use_the_reference_single_spacing(monkeypatch, dim):
+    """dim0 / dim1 workloads use ONE grid spacing, 8 / n_global_deriv, for both coordinates like
+    test_deriv (mpi_stencil2d_gt.cc:427-448): the initial field and the analytic derivative are those
+    of the CPU oracle built the reference's way, and err= is the oracle's."""
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    rt = runtime.init(use_cuda=False)
+    n_deriv, n_other = 32, 4096
+    nx, ny = (n_deriv, n_other) if dim == 0 else (n_other, n_deriv)
+    wl = Stencil2DWorkload(rt, nx, ny, mode=f"dim{dim}", impl="baseline", with_err=False)
+    wl.setup()
+    z_ref, actual, scale = oracle.init_stencil2d(n_deriv, n_other, dim, 0, 1)
+    assert wl.dx == wl.dy == 8.0 / n_deriv
+    assert torch.allclose(wl.z[0], z_ref, rtol=1e-14, atol=0.0)
+    assert torch.allclose(wl.analytic(0), actual, rtol=1e-14, atol=0.0)
+    wl.step()
+    want = oracle.err_norm(oracle.stencil2d_1d_5(z_ref, dim, scale), actual)
+    got = wl.err_norm(0)
+    # the other axis reaches 4096 * 0.25 = 1024, so rounding against y^2 (x^3) dominates: both see it
+    assert want > 1e-9 and abs(got - want) <= 0.5 * want + 1e-12
+    runtime.finalize()
+
+
 def test_native_engine_device_rule():
     """gmt_engine_default_device is the reference's set_rank_device rule (mpi_daxpy.cc:36-62);
     it makes no CUDA call, so it can be checked here through the C ABI."""

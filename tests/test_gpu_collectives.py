@@ -13,16 +13,21 @@ pytestmark = pytest.mark.gpu
 F64 = torch.float64
 
 
-@pytest.mark.parametrize("world,n", [(1, 1000), (2, 128), (4, 4096), (8, 1 << 16), (3, 1001), (8, 7)])
-def test_allgather_inplace_and_gather(dev, world, n):
+@pytest.mark.parametrize("mode", ["ll", "p2p"])
+@pytest.mark.parametrize("world,n", [(1, 1000), (2, 128), (4, 4096), (8, 1 << 16), (3, 1001), (8, 7), (8, 8192)])
+def test_allgather_inplace_and_gather(dev, world, n, mode):
     pc = PeerCollectives(VirtualSpace(world, dev), buf_doubles=world * n, spin_limit=1 << 24)
+    if mode == "ll" and n > pc.ll_gather_max:
+        with pytest.raises(ValueError):
+            pc.allgather_inplace(n, mode="ll")
+        mode = None   # the default picks the flag-based kernel for slices beyond 64 KiB
     for it in range(3):
         slices = [torch.rand(n, dtype=F64, device=dev) + r + 10 * it for r in range(world)]
         for r in range(world):
             b = pc.buffer(r)
             b.fill_(-1.0)
             b[r * n:(r + 1) * n] = slices[r]
-        pc.allgather_inplace(n)
+        pc.allgather_inplace(n, mode=mode)
         torch.cuda.synchronize()
         ref = torch.cat(slices)
         for r in range(world):
@@ -45,15 +50,34 @@ def test_allgather_inplace_and_gather(dev, world, n):
     assert pc.epochs() == [4] * world
 
 
-def test_allgather_from_separate_source(dev):
+@pytest.mark.parametrize("mode", ["ll", "p2p"])
+def test_allgather_from_separate_source(dev, mode):
     world, n = 4, 2048
     pc = PeerCollectives(VirtualSpace(world, dev), buf_doubles=world * n, spin_limit=1 << 24)
-    src = {r: torch.rand(n, dtype=F64, device=dev) for r in range(world)}
-    pc.allgather(n, src)
-    torch.cuda.synchronize()
-    ref = torch.cat([src[r] for r in range(world)])
+    for _ in range(3):
+        src = {r: torch.rand(n, dtype=F64, device=dev) for r in range(world)}
+        pc.allgather(n, src, mode=mode)
+        torch.cuda.synchronize()
+        ref = torch.cat([src[r] for r in range(world)])
+        for r in range(world):
+            assert torch.equal(pc.buffer(r), ref)
+    pc.check_status()
+
+
+def test_ll_gather_and_daxpy_report_a_too_small_staging_area(dev):
+    """The raw entry points cannot see stage_cap from the host: a call that needs more LL cells than
+    the descriptor provides must write nothing out of bounds and say so in the status word."""
+    from gpu_mpi_tests_b200.ops._lib import lib
+    from gpu_mpi_tests_b200.parallel.collectives import CollectiveTimeout
+    world, n = 2, 4096
+    pc = PeerCollectives(VirtualSpace(world, dev), buf_doubles=world * n, stage_cap=2048, spin_limit=1 << 20)
     for r in range(world):
-        assert torch.equal(pc.buffer(r), ref)
+        pc.buffer(r).fill_(-1.0)
+    lib.gmt_allgather_f64(pc._ranks_dev.data_ptr(), world, n, 0, 2, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    with pytest.raises(CollectiveTimeout, match="stage_cap"):
+        pc.check_status()
+    assert all(float(pc.buffer(r).max()) == -1.0 for r in range(world))
 
 
 @pytest.mark.parametrize("algo", ["ll", "one_shot", "two_shot"])
@@ -73,18 +97,32 @@ def test_allreduce(dev, algo, world, n):
     pc.check_status()
 
 
-@pytest.mark.parametrize("world,n", [(1, 1024), (2, 1 << 20), (8, (1 << 18) + 6), (4, 1000)])
-def test_daxpy_allreduce(dev, world, n):
+@pytest.mark.parametrize("misalign", [0, 1])
+@pytest.mark.parametrize("world,n", [(1, 1024), (2, 1 << 20), (8, (1 << 18) + 6), (4, 1000), (1, 1 << 24), (3, 3), (8, 5 * 4096 * 37 + 13)])
+def test_daxpy_allreduce(dev, world, n, misalign):
+    """One partial per CTA travels as an LL cell to every rank; the cases cover one chunk per CTA,
+    several chunks per CTA (a cooperative launch of 8 ranks leaves 37 CTAs each), the scalar tail,
+    n smaller than a vector, and operands that are not 32-byte aligned (scalar path)."""
+    if misalign and n > (1 << 22):
+        pytest.skip("the scalar path is covered by the smaller cases")
     pc = PeerCollectives(VirtualSpace(world, dev), spin_limit=1 << 24)
     xs, ys, outs = {}, {}, {}
     for r in range(world):
-        xs[r], ys[r] = oracle.daxpy_init_scaled(n, dev)
+        x, y = oracle.daxpy_init_scaled(n, dev)
+        if misalign:   # 8-byte offset views: not 32-byte aligned
+            xb, yb = torch.empty(n + 1, dtype=F64, device=dev), torch.empty(n + 1, dtype=F64, device=dev)
+            xb[1:].copy_(x)
+            yb[1:].copy_(y)
+            x, y = xb[1:], yb[1:]
+        xs[r], ys[r] = x, y
         outs[r] = torch.zeros(1, dtype=F64, device=dev)
     pc.daxpy_allreduce(2.0, xs, ys, outs)
     torch.cuda.synchronize()
     expect = oracle.daxpy_scaled_expected_allsum(n, world)  # ALLSUM of mpi_daxpy_nvtx.cc:310
     for r in range(world):
         assert outs[r].item() == pytest.approx(expect, rel=1e-12)
+        assert outs[r].item() == pytest.approx(world * float(torch.sum(xs[r])), rel=1e-12)   # torch fp64 reference
+        assert torch.equal(outs[r], outs[0])                 # fixed summation order: same bits on every rank
         assert float((ys[r] - xs[r]).abs().max()) < 1e-15  # y = 2x - x = x
     # second call on the updated y: y = 2x + x = 3x
     pc.daxpy_allreduce(2.0, xs, ys, outs)
@@ -108,6 +146,60 @@ def test_axis_sum_allreduce(dev, axis):
     for r in range(world):
         assert float((out[r] - ref).abs().max()) <= 1e-12 * float(ref.abs().max())
     pc.check_status()
+
+
+@pytest.mark.parametrize("axis", [0, 1])
+def test_axis_sum_allreduce_large_takes_the_one_shot_path(dev, axis):
+    """n_out x world beyond 2^18 cells: the kernel itself switches from LL cells to the staged one-shot
+    (the C entry point used to keep LL up to 32 Ki doubles whatever the world size)."""
+    world = 8
+    n_out = (1 << 15) + 8            # x 8 ranks > 2^18
+    nx, ny = (4, n_out) if axis == 0 else (n_out, 3)
+    pc = PeerCollectives(VirtualSpace(world, dev), stage_cap=n_out, spin_limit=1 << 24)
+    z = {r: torch.rand(ny, nx, dtype=F64, device=dev) for r in range(world)}
+    out = {r: torch.zeros(n_out, dtype=F64, device=dev) for r in range(world)}
+    for _ in range(2):
+        pc.axis_sum_allreduce(z, axis, out, n_out)
+    torch.cuda.synchronize()
+    ref = sum((z[r].sum(dim=1) if axis == 0 else z[r].sum(dim=0))[:n_out] for r in range(world))
+    for r in range(world):
+        assert float((out[r] - ref).abs().max()) <= 1e-12 * float(ref.abs().max())
+        assert torch.equal(out[r], out[0])
+    pc.check_status()
+
+
+@pytest.mark.parametrize("axis", [0, 1])
+def test_axis_sum_allreduce_on_a_mostly_occupied_gpu(dev, axis):
+    """The LL flavour must not depend on its whole grid being resident: whoever waits for a cell
+    waits for another RANK's push only.  Another stream holds all but a few SMs for 200 ms; the
+    collective (a plain, non-cooperative launch of several hundred CTAs) has to finish long before
+    that kernel does instead of spinning on cells that CTAs still waiting for an SM would push."""
+    from gpu_mpi_tests_b200.ops._lib import lib
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    n_out = 4096
+    nx, ny = (64, n_out) if axis == 0 else (n_out, 64)
+    pc = PeerCollectives(VirtualSpace(1, dev), stage_cap=n_out, spin_limit=1 << 26)
+    z = {0: torch.rand(ny, nx, dtype=F64, device=dev)}
+    out = {0: torch.zeros(n_out, dtype=F64, device=dev)}
+    pc.axis_sum_allreduce(z, axis, out, n_out)     # warm: module loaded, descriptors bound
+    torch.cuda.synchronize()
+    out[0].zero_()
+    hog, work = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    hog_done = torch.cuda.Event()
+    with torch.cuda.stream(hog):
+        lib.gmt_debug_occupy(2 * (sms - 4), 200_000_000, hog.cuda_stream)
+        hog_done.record()
+    import time
+    time.sleep(0.02)                               # the hog is on the SMs now
+    with torch.cuda.stream(work):
+        pc.axis_sum_allreduce(z, axis, out, n_out)
+    work.synchronize()
+    finished_early = not hog_done.query()
+    torch.cuda.synchronize()
+    pc.check_status()
+    ref = (z[0].sum(dim=1) if axis == 0 else z[0].sum(dim=0))[:n_out]
+    assert float((out[0] - ref).abs().max()) <= 1e-12 * float(ref.abs().max())
+    assert finished_early, "the collective waited for the other stream's kernel to leave the GPU"
 
 
 def test_barrier_and_timeout(dev):

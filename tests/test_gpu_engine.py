@@ -25,7 +25,7 @@ def close(a, b, rtol=1e-10):
     return bool(((a - b).abs() <= rtol * (1.0 + b.abs())).all())
 
 
-@pytest.mark.parametrize("px,py,gx,gy", [(2, 2, 2, 2), (4, 1, 2, 0), (1, 3, 0, 2), (1, 1, 2, 2)])
+@pytest.mark.parametrize("px,py,gx,gy", [(2, 2, 2, 2), (4, 1, 2, 0), (1, 3, 0, 2), (1, 1, 2, 2), (3, 3, 2, 2)])
 def test_engine_matches_python_plan(px, py, gx, gy):
     """Same grid through the C++ engine (all ranks on GPU 0, one cooperative launch) and through
     the Python plan on virtual ranks: same result arrays, same landed ghosts, same error norm."""
@@ -52,6 +52,32 @@ def test_engine_matches_python_plan(px, py, gx, gy):
         assert torch.equal(eng.array(r, "z"), plan.z[r]), f"rank {r}: ghosts"
         assert eng.err_norm(r) == pytest.approx(plan.err_norm(r), rel=0.1, abs=1e-9)
         assert eng.err_norm(r) < 1e-3
+    # the exchange alone through the engine: ghosts poisoned again, then refreshed without a sweep
+    for r in range(world):
+        z = eng.array(r, "z")
+        if gx:
+            z[:, :2] = 1e30
+            z[:, -2:] = 1e30
+        if gy:
+            z[:2, :] = 1e30
+            z[-2:, :] = 1e30
+    torch.cuda.synchronize()
+    eng.exchange()
+    eng.synchronize()
+    eng.check()
+    for r in range(world):
+        z, ref = eng.array(r, "z"), plan.z[r]
+        cx, cy = r % px, r // px
+        ys, xs = slice(gy, gy + ny), slice(gx, gx + nx)
+        if gx and cx > 0:
+            assert torch.equal(z[ys, :2], ref[ys, :2])
+        if gx and cx < px - 1:
+            assert torch.equal(z[ys, -2:], ref[ys, -2:])
+        if gy and cy > 0:
+            assert torch.equal(z[:2, xs], ref[:2, xs])
+        if gy and cy < py - 1:
+            assert torch.equal(z[-2:, xs], ref[-2:, xs])
+    assert eng.time_exchanges(3, 1) > 0.0
     eng.close()
 
 

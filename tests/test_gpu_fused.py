@@ -60,6 +60,9 @@ CASES_2D = [
     (2, 2, 2048, 256, 2, 2),     # BASELINE config 3 shape: 4 neighbours
     (4, 2, 1024, 384, 2, 2),
     (3, 2, 36, 50, 2, 2),
+    (3, 3, 1028, 300, 2, 2),     # the centre rank has FOUR live faces
+    (3, 4, 2048, 130, 2, 2),     # two ranks with four live faces, several row tiles
+    (2, 1, 64, 66000, 2, 0),     # >= 64 x-face chunks: exported in groups of 4 per fence
 ]
 
 
@@ -85,6 +88,145 @@ def test_fused_stencil2d(dev, px, py, nx, ny, gx, gy):
         else:
             ref = local.stencil2d(z, 1, plan.sy)
         assert close(plan.out[r], ref)
+
+
+def _ghost_pairs(plan, r):
+    """(ghost view of rank r, matching boundary view of the neighbour) for every live side."""
+    z, gx, gy, nx, ny = plan.z[r], plan.gx, plan.gy, plan.nx, plan.ny
+    g = plan.grids[r]
+    ys, xs = slice(gy, gy + ny), slice(gx, gx + nx)
+    out = []
+    for side in range(4):
+        if not (gx if side < 2 else gy):
+            continue
+        nb = g.neighbour(side)
+        if nb < 0:
+            continue
+        o = plan.z[nb]
+        if side == 0:
+            out.append((side, z[ys, 0:2], o[ys, nx:nx + 2]))
+        elif side == 1:
+            out.append((side, z[ys, gx + nx:gx + nx + 2], o[ys, gx:gx + 2]))
+        elif side == 2:
+            out.append((side, z[0:2, xs], o[ny:ny + 2, xs]))
+        else:
+            out.append((side, z[gy + ny:gy + ny + 2, xs], o[gy:gy + 2, xs]))
+    return out
+
+
+EXCH_2D = CASES_2D + [
+    (2, 2, 16384, 16384 // 8, 2, 2),   # flagship tile width, many row tiles per face
+    (1, 1, 1024, 256, 2, 2),
+]
+
+
+@pytest.mark.parametrize("px,py,nx,ny,gx,gy", EXCH_2D)
+@pytest.mark.parametrize("periodic", [False, True])
+def test_halo_exchange2d_alone(dev, px, py, nx, ny, gx, gy, periodic):
+    """The exchange as a callable of its own (boundary_exchange_x/_y, mpi_stencil2d_gt.cc:136-373):
+    poisoned ghosts become the neighbours' boundary values, nothing else in the array and nothing
+    in `out` changes, and it can be mixed with fused steps on the same plan."""
+    if periodic and nx * ny > (1 << 22):
+        pytest.skip("one big case is enough")
+    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, gx, gy, with_err=False, spin_limit=1 << 24,
+                          periodic=periodic)
+    plan.init_analytic(poison=1e30)
+    for r in plan.ranks:
+        plan.out[r].fill_(-7.0)
+    before = {r: plan.z[r].clone() for r in plan.ranks}
+    for it in range(3):
+        for r in plan.ranks:   # the field changes between calls: both inbox parities are exercised
+            plan.z[r][gy:gy + ny, gx:gx + nx].add_(float(it + r))
+            before[r][gy:gy + ny, gx:gx + nx].add_(float(it + r))
+        plan.exchange()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [3] * (px * py)
+    for r in plan.ranks:
+        assert float(plan.out[r].min()) == float(plan.out[r].max()) == -7.0     # no sweep happened
+        pairs = _ghost_pairs(plan, r)
+        if periodic:
+            assert len(pairs) == 2 * (bool(gx) + bool(gy))
+        for side, mine, theirs in pairs:
+            assert torch.equal(mine, theirs), f"rank {r} side {side}"
+        # everything that is not a live ghost cell is untouched
+        z, b = plan.z[r], before[r]
+        mask = torch.ones_like(z, dtype=torch.bool)
+        g = plan.grids[r]
+        if gx and g.neighbour(0) >= 0:
+            mask[gy:gy + ny, 0:2] = False
+        if gx and g.neighbour(1) >= 0:
+            mask[gy:gy + ny, gx + nx:] = False
+        if gy and g.neighbour(2) >= 0:
+            mask[0:2, gx:gx + nx] = False
+        if gy and g.neighbour(3) >= 0:
+            mask[gy + ny:, gx:gx + nx] = False
+        assert torch.equal(z[mask], b[mask]), f"rank {r}: exchange touched cells outside the live ghost strips"
+    # mixed with a fused step on the same plan (same epoch counter and inbox parities)
+    plan.step()
+    plan.exchange()
+    plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [6] * (px * py)
+    if not periodic:
+        for r in plan.ranks:
+            ref = (local.stencil2d_xy(plan.z[r], plan.sx, plan.sy) if gx and gy else
+                   local.stencil2d(plan.z[r], 0 if gx else 1, plan.sx if gx else plan.sy))
+            assert close(plan.out[r], ref)
+
+
+@pytest.mark.parametrize("world,n", [(1, 4096), (2, 64), (5, 4096 * 3 + 2), (8, 65536)])
+def test_halo_exchange1d_alone(dev, world, n):
+    """boundary_exchange (mpi_stencil_gt.cc:83-122) as a callable: 16 bytes per side."""
+    plan = FusedStencil1D(VirtualSpace(world, dev), n, with_err=False, spin_limit=1 << 24)
+    plan.init_analytic()
+    for r in plan.ranks:
+        plan.out[r].fill_(-7.0)
+        if r > 0:
+            plan.z[r][:2] = 1e30
+        if r < world - 1:
+            plan.z[r][-2:] = 1e30
+    for it in range(4):
+        for r in plan.ranks:
+            plan.z[r][2:-2].add_(float(it + r))
+        plan.exchange()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [4] * world
+    for r in plan.ranks:
+        assert float(plan.out[r].min()) == -7.0
+        if r > 0:
+            assert torch.equal(plan.z[r][:2], plan.z[r - 1][-4:-2])
+        if r < world - 1:
+            assert torch.equal(plan.z[r][-2:], plan.z[r + 1][2:4])
+    plan.step()
+    plan.exchange()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [6] * world
+
+
+def test_periodic_grid_gives_every_rank_four_live_faces(dev):
+    """Grid2D(periodic=True): a 4 x 2 grid (the 8-GPU shape) exchanges all four faces on every rank;
+    ghosts equal the wrapped neighbours' boundary values after fused steps with a changing field."""
+    px, py, nx, ny = 4, 2, 1024, 256
+    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, 2, 2, with_err=False, spin_limit=1 << 24,
+                          periodic=True)
+    plan.init_analytic(poison=1e30)
+    assert all(plan.halo_bytes_out(r) == 2 * 8 * 2 * (nx + ny) for r in plan.ranks)
+    for it in range(4):
+        for r in plan.ranks:
+            plan.z[r][2:-2, 2:-2].mul_(1.0 + 1e-3 * ((it + r) % 5))
+        plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    for r in plan.ranks:
+        pairs = _ghost_pairs(plan, r)
+        assert len(pairs) == 4
+        for side, mine, theirs in pairs:
+            assert torch.equal(mine, theirs), f"rank {r} side {side}"
+        assert close(plan.out[r], local.stencil2d_xy(plan.z[r], plan.sx, plan.sy))
 
 
 def test_fused_values_change_between_steps(dev):
@@ -161,13 +303,46 @@ def test_host_fed_sides_behave_like_a_neighbour(dev, px, py):
             if rr == r:  # the kernel landed the host values in the array's own ghost cells
                 assert torch.equal(fed.plan.ghost_view(r, side), ref.plan.ghost_view(r, side))
     # new boundary values from the host reach the array
-    for h, _box in fed._fed:
+    for h in fed.host_inputs(0):
         h.add_(1.0)
     fed.step_e2e()
     torch.cuda.synchronize()
     r0 = fed.ranks[0]
     side0 = [s for (rr, s) in fed.plan.host_sides if rr == r0][0]
     assert torch.allclose(fed.plan.ghost_view(r0, side0), ref.plan.ghost_view(r0, side0) + 1.0)
+
+
+def test_pipelined_e2e_lags_one_step_and_tracks_new_inputs(dev):
+    """step_e2e_pipelined(): the result returned by call k is step k-1's; inputs written into the
+    buffers host_inputs() hands out reach exactly the step they were written for (two alternating
+    sets of pinned buffers / flag sources / result words)."""
+    from gpu_mpi_tests_b200.models.stencil2d import Stencil2DWorkload
+    from gpu_mpi_tests_b200.parallel import runtime
+    rt = runtime.init()
+    nx, ny = 2048, 384
+    sync = Stencil2DWorkload(rt, nx, ny, mode="grid", impl="fused", space=VirtualSpace(1, dev), grid=(1, 1),
+                             spin_limit=1 << 26, host_fed=True)
+    pipe = Stencil2DWorkload(rt, nx, ny, mode="grid", impl="fused", space=VirtualSpace(1, dev), grid=(1, 1),
+                             spin_limit=1 << 26, host_fed=True)
+    sync.setup()
+    pipe.setup()
+    base = [h.clone() for h in pipe.host_inputs(0)]
+    want, got = [], []
+    for k in range(7):
+        bump = 0.125 * k                      # a different boundary value every step: err_norm changes with it
+        for h, b in zip(sync.host_inputs(0), base):
+            h.copy_(b + bump)
+        want.append(sync.step_e2e())
+        for h, b in zip(pipe.host_inputs(), base):
+            h.copy_(b + bump)
+        got.append(pipe.step_e2e_pipelined())
+    got.append(pipe.e2e_flush())
+    torch.cuda.synchronize()
+    pipe.check()
+    assert got[0] is None
+    assert got[1:] == pytest.approx(want, rel=1e-6, abs=1e-12)
+    assert want[-1] > 10 * want[0]            # the bumped boundary values really reached the kernel
+    assert pipe.plan.epochs() == [pipe.plan.steps]
 
 
 @pytest.mark.parametrize("oneshot", ["0", "1"])

@@ -46,6 +46,11 @@ def test_noalloc_matches_caller_scratch_entry_point_twice_in_a_row(native, dev, 
         assert torch.equal(y_new, y_ref), f"call {call}: y differs"
         ref = s_ref.item()
         assert abs(s_new.item() - ref) <= RTOL * abs(ref) + 1e-300, f"call {call}: {s_new.item()} vs {ref}"
+        # and against plain PyTorch fp64 arithmetic, not only against the sibling kernel
+        y_torch = a * x + y0
+        assert float((y_new - y_torch).abs().max()) <= 1e-15 * (1.0 + float(y_torch.abs().max()))
+        t_sum = y_torch.sum().item()
+        assert abs(s_new.item() - t_sum) <= RTOL * max(abs(t_sum), float(y_torch.abs().sum().item()) * 1e-3) + 1e-300
         y0 = y_ref  # the second call starts from the first call's result
 
 
@@ -80,3 +85,22 @@ def test_noalloc_rejects_sizes_beyond_the_fixed_scratch(native, dev):
     assert rc == -2  # GMT_ETOOBIG
     msg = native.last_error()
     assert "exceeds the fixed scratch capacity" in msg and str(max_n) in msg
+
+
+def test_noalloc_on_a_second_device(native):
+    """Every GPU holds its own copy of the array; the address is looked up per device."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    noalloc = native.raw("gmt_daxpy_sum_noalloc_f64")
+    for d in (1, 0, 1):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            x = torch.rand(100_003, dtype=F64, device=dev)
+            y = torch.rand(100_003, dtype=F64, device=dev)
+            ref = 1.5 * x + y
+            s = torch.zeros(1, dtype=F64, device=dev)
+            stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            assert noalloc(x.numel(), 1.5, _ptr(x), _ptr(y), _ptr(s), stream) == 0, native.last_error()
+            torch.cuda.synchronize(dev)
+            assert float((y - ref).abs().max()) < 1e-14
+            assert abs(s.item() - ref.sum().item()) <= RTOL * abs(ref.sum().item())
