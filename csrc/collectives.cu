@@ -632,6 +632,10 @@ __global__ void __launch_bounds__(32) barrier_kernel(const gmt_coll_rank* __rest
 }
 
 // ============================================================ launch helpers
+// Test hook: single-rank launches get up to `factor` times more CTAs than can be resident at once, so
+// that a kernel which (wrongly) waited for a sibling CTA of its own grid would expire its bounded spin.
+static int g_debug_grid_factor = 1;
+
 static int coll_grid(const void* kernel, int64_t work_ctas, int n_ranks, int* grid)
 {
   int occ = 0;
@@ -639,6 +643,7 @@ static int coll_grid(const void* kernel, int64_t work_ctas, int n_ranks, int* gr
   if (occ < 1) occ = 1;
   int64_t cap = (int64_t)sm_count() * occ;
   if (n_ranks > 1) cap /= n_ranks;
+  else cap *= g_debug_grid_factor;
   GMT_REQUIRE(cap >= 1, GMT_ETOOBIG, "too many virtual ranks (%d) for one cooperative launch", n_ranks);
   *grid = (int)std::max<int64_t>(1, std::min<int64_t>(cap, work_ctas));
   return 0;
@@ -750,6 +755,13 @@ int gmt_axis_sum_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int6
   if (rc) return rc;
   void* args[] = {(void*)&ranks_dev, (void*)&nx, (void*)&ny, (void*)&ld, (void*)&axis, (void*)&n_out};
   return coll_launch(k, grid, n_ranks, args, as_stream(stream));
+}
+
+int gmt_debug_set_grid_factor(int factor)
+{
+  GMT_REQUIRE(factor >= 1 && factor <= 64, GMT_EINVAL, "gmt_debug_set_grid_factor: factor must be 1..64");
+  gmt::g_debug_grid_factor = factor;
+  return 0;
 }
 
 size_t gmt_coll_stage_bytes(int world, int64_t stage_cap)

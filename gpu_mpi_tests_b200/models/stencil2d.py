@@ -88,8 +88,9 @@ class Stencil2DWorkload:
         if self.host_fed:
             # the kernel takes the host-fed ghosts from its inbox: start it off with the analytic values
             for (r, side), (off, cnt, _f) in self.plan.host_sides.items():
-                self.plan.hostbox[r][off:off + cnt].view(self.plan.host_side_shape(side)).copy_(
-                    self.plan.ghost_view(r, side))
+                for p in range(2):
+                    self.plan.hostbox[r][p][off:off + cnt].view(self.plan.host_side_shape(side)).copy_(
+                        self.plan.ghost_view(r, side))
 
     def step(self) -> None:
         if self.host_fed:
@@ -174,20 +175,21 @@ class Stencil2DWorkload:
             if box is None:
                 continue
             for slot in range(2):
-                h = torch.empty(box.numel(), dtype=F64, pin_memory=True)
+                h = torch.empty(box.shape[1], dtype=F64, pin_memory=True)
                 for (rr, side), (off, cnt, _f) in plan.host_sides.items():
                     if rr == r:
                         # inbox layouts: x faces [2*j + r] == row-major (ny, 2); y faces [r*nx + i] == (2, nx)
                         h[off:off + cnt].view(plan.host_side_shape(side)).copy_(plan.ghost_view(rr, side))
                 self._fed[slot].append((h, box))
-            total += box.numel()
+            total += box.shape[1]
         self._bc_total = total
         self._host_bc = self._fed[0][0][0] if self._fed[0] else torch.empty(1, dtype=F64, pin_memory=True)
         self._err_dev = torch.zeros(len(self.ranks), dtype=F64, device=self.device)
         self._err_host = torch.zeros(len(self.ranks), dtype=F64, pin_memory=True)
         self._err_host2 = [self._err_host, torch.zeros(len(self.ranks), dtype=F64, pin_memory=True)]
         self._graph = None
-        self._graphs = [None, None]
+        self._graphs = [None, None]     # synchronous step: one captured graph per inbox parity
+        self._warmed = False
         self._graph_failed = False
         self._side_stream = torch.cuda.Stream(device=self.device)
         self._pipe_events = [None, None]
@@ -256,9 +258,10 @@ class Stencil2DWorkload:
             main = torch.cuda.current_stream()
             side = self._side_stream
             side.wait_stream(main)
+            par = self.plan.next_parity()
             with torch.cuda.stream(side):
                 for h, box in self._fed[slot]:
-                    box.copy_(h, non_blocking=True)
+                    box[par].copy_(h, non_blocking=True)
                 for r in self.ranks:
                     self.plan.publish_host_sides_by_copy(r, slot)   # copy engine: needs no SM slot
             self.plan.step()
@@ -276,12 +279,11 @@ class Stencil2DWorkload:
         self._err_host.copy_(self._err_dev, non_blocking=True)             # one D2H
 
     def _capture(self, slot: int):
-        """Capture one end-to-end step (slot's host buffers) in a CUDA graph; None when that fails."""
-        steps_before = None
+        """Capture one end-to-end step (slot's host buffers, the inbox parity of the NEXT step) in a
+        CUDA graph; None when that fails.  Call after at least one eager step (kernels loaded)."""
+        steps_before = self.plan.steps
         try:
-            self._e2e_body(slot)                  # warm-up outside capture
             torch.cuda.synchronize(self.device)
-            steps_before = self.plan.steps
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._e2e_body(slot)
@@ -289,10 +291,9 @@ class Stencil2DWorkload:
             return g
         except Exception:  # noqa: BLE001 - capture is an optimisation, never a requirement
             self._graph_failed = True
-            if steps_before is not None:
-                # whatever ran inside the failed capture launched nothing: the host step count
-                # must not run ahead of the device epoch (host-fed flags are published from it)
-                self.plan.steps = steps_before
+            # whatever ran inside the failed capture launched nothing: the host step count must not
+            # run ahead of the device epoch (host-fed flags are published from it)
+            self.plan.steps = steps_before
             torch.cuda.synchronize(self.device)
             return None
 
@@ -314,17 +315,25 @@ class Stencil2DWorkload:
         if self._host_bc is None:
             self._prepare_e2e()
         cuda = self.device.type == "cuda"
-        if self._graphable(use_graph) and self._graph is None:
-            self._graph = self._capture(0)
-            if self.host_fed:
-                self._graphs[0] = self._graph
-        if self._graphable(use_graph) and self._graph is not None:
-            if self.host_fed:
-                self.plan.refresh_host_epoch(0)
-            self._graph.replay()
-            self.plan.steps += 1
-        else:
-            self._e2e_body(0)
+        replayed = False
+        if self._graphable(use_graph) and getattr(self, "_warmed", False):
+            # host-fed plans alternate between two inboxes by epoch parity: one graph per parity
+            par = self.plan.next_parity() if self.host_fed else 0
+            graphs = self._graphs if self.host_fed else getattr(self, "_graphs_plain", None)
+            if graphs is None:
+                graphs = self._graphs_plain = [None, None]
+            if graphs[par] is None:
+                graphs[par] = self._capture(0)
+            if graphs[par] is not None:
+                if self.host_fed:
+                    self.plan.refresh_host_epoch(0)
+                graphs[par].replay()
+                self.plan.steps += 1
+                self._graph = graphs[par]
+                replayed = True
+        if not replayed:
+            self._e2e_body(0)      # the first call runs eagerly (and loads the kernels)
+            self._warmed = True
         if cuda:
             torch.cuda.current_stream().synchronize()
         return self._result(self._err_host)
@@ -332,52 +341,62 @@ class Stencil2DWorkload:
     def step_e2e_pipelined(self):
         """The same step for a loop that can live with a result that lags ONE step: enqueue this
         step (upload of its boundary values from the pinned buffers `host_inputs()` returned, fused
-        kernel, copy of its error word to pinned memory) and only then wait for and return the
-        PREVIOUS step's err_norm (None on the first call).  The host round trip -- wake-up after the
-        synchronise, Python, graph launch, ~30 us -- is thereby spent while the GPU already runs the
-        next step, instead of between steps.  Everything the host writes per step exists twice and
-        alternates, so a step that is still in the queue never has its inputs, flag epoch or result
-        word overwritten.  `e2e_flush()` returns the last step's result.  The first call
-        captures the two CUDA graphs (and runs one eager warm-up step for each).  host_fed fused
-        plans only; other plans fall back to the synchronous step_e2e()."""
+        kernel, its error word) and only then wait for and return the PREVIOUS step's err_norm (None
+        on the first call).  The host round trip -- wake-up after the synchronise, Python, launch,
+        ~30 us -- is thereby spent while the GPU already runs the next step, instead of between steps.
+          * No CUDA graph and no copy node behind the kernel: the kernel's last CTA stores the error
+            word straight into pinned host memory (mapped into the device's address space), the
+            kernels of consecutive steps sit back to back in the main stream, and the uploads run on
+            a side stream into the inbox of the step's epoch parity -- i.e. while the previous step's
+            kernel is still running on the other parity's inbox.  The kernel needs no stream
+            dependency on the upload: its boundary tiles wait for the flags the upload publishes,
+            like for a neighbour's.
+          * Everything the host writes per step exists twice and alternates (boundary values, flag
+            epoch source, result word), so a step that is still in the queue never has its inputs
+            or result overwritten.
+        `e2e_flush()` returns the last step's result.  host_fed fused plans hosting one rank only;
+        other plans fall back to the synchronous step_e2e()."""
         if self._host_bc is None:
             self._prepare_e2e()
-        if not (self.host_fed and self._graphable(True)):
+        if not (self.host_fed and self.device.type == "cuda" and self.impl == "fused" and self.with_err):
             return self.step_e2e()
+        plan = self.plan
+        results = plan.host_result_slots()
         slot = self._pipe_calls % 2
-        if self._graphs[0] is None or self._graphs[1] is None:
-            # first use: capture one graph per slot (each capture is preceded by one eager warm-up step)
-            self.e2e_flush()
-            for k in range(2):
-                if self._graphs[k] is None:
-                    self._graphs[k] = self._capture(k)
-            if self._graphs[0] is None or self._graphs[1] is None:
-                self._graphs = [None, None]
-                return self.step_e2e()
-            self._graph = self._graphs[0]
-        self.plan.refresh_host_epoch(slot)
-        self._graphs[slot].replay()
-        self.plan.steps += 1
+        prev = slot ^ 1
+        main, side = torch.cuda.current_stream(), self._side_stream
+        if self._pipe_calls == 0:
+            side.wait_stream(main)
+        # (no wait for the previous kernel: its inbox is the other parity's, and the kernel that last read
+        # THIS parity's inbox, two steps back, was synchronised with by the previous call)
+        par = plan.next_parity()
+        with torch.cuda.stream(side):
+            for h, box in self._fed[slot]:
+                box[par].copy_(h, non_blocking=True)
+            for r in self.ranks:
+                plan.publish_host_sides_by_copy(r, slot)   # copy engine: needs no SM slot
+        plan.step(result_slot=slot)
         if self._pipe_events[slot] is None:
             self._pipe_events[slot] = torch.cuda.Event()
-        self._pipe_events[slot].record()
+        self._pipe_events[slot].record(main)
         self._pipe_calls += 1
-        prev = slot ^ 1
-        if self._pipe_calls < 2 or self._pipe_events[prev] is None:
+        if self._pipe_calls < 2:
             return None
         self._pipe_events[prev].synchronize()
-        return self._result(self._err_host2[prev])
+        return self._result(results[prev][:, 0])
 
     def e2e_flush(self):
         """Wait for the step enqueued by the last step_e2e_pipelined() call; returns its err_norm
-        (None when nothing is outstanding)."""
+        (None when nothing is outstanding).  Afterwards the main stream also waits for the side
+        stream, so any later work on it sees the uploads complete."""
         if not self.host_fed or self._host_bc is None or self._pipe_calls == 0:
             return None
         last = (self._pipe_calls - 1) % 2
         if self._pipe_events[last] is None:
             return None
         self._pipe_events[last].synchronize()
-        return self._result(self._err_host2[last])
+        torch.cuda.current_stream().wait_stream(self._side_stream)
+        return self._result(self.plan.host_result_slots()[last][:, 0])
 
     # ------------------------------------------------------------------ validation
     def analytic(self, rank: int) -> torch.Tensor:

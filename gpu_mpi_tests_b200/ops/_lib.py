@@ -137,6 +137,7 @@ _SIGS = {
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),
     "gmt_debug_set_push_delay": (None, [C.c_uint]),
     "gmt_debug_occupy": (None, [C.c_int, C.c_ulonglong, c_ptr]),
+    "gmt_debug_set_grid_factor": (None, [C.c_int]),
     "gmt_publish_epoch_flags": (None, [c_ptr, c_i64, c_ptr, c_ptr]),
     "gmt_allgather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_gather_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),

@@ -201,7 +201,9 @@ class FusedStencil2D(_PlanBase):
             fed = [side for side in range(4) if (gx if side < 2 else gy) and g.neighbour(side) < 0] if host_fed else []
             total = sum(2 * (ny if side < 2 else nx) for side in fed)
             if fed:
-                self.hostbox[r] = torch.zeros(total, dtype=F64, device=self.device)
+                # one inbox per epoch parity, like the peers' inboxes: the upload for step s+1 may then
+                # run while the kernel of step s is still reading step s's values
+                self.hostbox[r] = torch.zeros(2, total, dtype=F64, device=self.device)
                 self._hostflags[r] = torch.zeros(4, max(nfx, nfy), dtype=torch.int64, device=self.device)
                 # two pinned sources: a pipelined caller enqueues step s+1 before step s has run
                 self._hostflags_pinned[r] = [torch.zeros(4, max(nfx, nfy), dtype=torch.int64, pin_memory=True)
@@ -220,9 +222,8 @@ class FusedStencil2D(_PlanBase):
                 if side in fed:
                     cnt = 2 * (ny if side < 2 else nx)
                     s.has[side] = 2
-                    box = self.hostbox[r][off:off + cnt]
-                    # one buffer for both parities: host feeds are stream-ordered between steps
-                    s.my_inbox[side][0] = s.my_inbox[side][1] = box.data_ptr()
+                    for p in range(2):
+                        s.my_inbox[side][p] = self.hostbox[r][p][off:off + cnt].data_ptr()
                     nflags = nfx if side < 2 else nfy
                     s.my_flag[side] = self._hostflags[r][side].data_ptr()
                     self.host_sides[(r, side)] = (off, cnt, self._hostflags[r][side][:nflags])
@@ -260,10 +261,31 @@ class FusedStencil2D(_PlanBase):
             a += (self.sy * self.dy) * 2.0 * ys[:, None]
         return a
 
-    def step(self) -> None:
-        lib.gmt_fused_stencil2d_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.nx, self.ny, self.gx, self.gy,
+    def step(self, result_slot: int | None = None) -> None:
+        """One fused exchange + stencil step.  result_slot (0/1, after host_result_slots()): the error
+        word of this step goes straight into that pinned host word instead of device memory."""
+        desc = self._ranks_dev if result_slot is None else self._ranks_dev_slot[result_slot]
+        lib.gmt_fused_stencil2d_f64(desc.data_ptr(), len(self.ranks), self.nx, self.ny, self.gx, self.gy,
                                     int(self.with_err), torch.cuda.current_stream().cuda_stream)
         self.steps += 1
+
+    def host_result_slots(self) -> list:
+        """Two pinned host tensors (one fp64 word per hosted rank each) and, for each, a copy of the
+        rank descriptors whose err_sumsq points at it: pinned memory is mapped into the device's
+        address space (unified addressing), so the kernel's last CTA stores the step's error word
+        straight to the host and no device-to-host copy has to be queued behind the kernel.  Two
+        slots, because a pipelined caller reads step s's word while step s+1 is already running."""
+        if getattr(self, "_result_host", None) is None:
+            self._result_host = [torch.zeros(len(self.ranks), 8, dtype=F64, pin_memory=True) for _ in range(2)]
+            self._ranks_dev_slot = []
+            for slot in range(2):
+                structs = []
+                for k, s0 in enumerate(self._structs):
+                    s = type(s0).from_buffer_copy(bytes(s0))   # ctypes structures with pointers cannot be copy.copy()ed
+                    s.err_sumsq = self._result_host[slot][k].data_ptr()
+                    structs.append(s)
+                self._ranks_dev_slot.append(_structs_to_device(structs, self.device))
+        return self._result_host
 
     def exchange(self) -> None:
         """The halo exchange alone (boundary_exchange_x / _y, mpi_stencil2d_gt.cc:136-373): afterwards
@@ -302,10 +324,18 @@ class FusedStencil2D(_PlanBase):
         for rank in self._hostflags_pinned:
             self._hostflags_pinned[rank][slot].fill_(self.steps + 1)
 
+    def next_parity(self) -> int:
+        """Inbox parity (index into hostbox[rank]) the NEXT step or exchange will read."""
+        return (self.steps + 1) & 1
+
     def publish_host_sides(self, rank: int) -> None:
         """Kernel flavour, for use on the SAME stream BEFORE the fused kernel (plain step() of a
-        host-fed plan): mark the host-fed sides of the step about to run as arrived."""
+        host-fed plan without new host data): the next step's inbox takes over what the last one
+        held, and the host-fed sides of the step about to run are marked as arrived."""
         k = self._slot(rank)
+        if rank in self.hostbox:
+            p = self.next_parity()
+            self.hostbox[rank][p].copy_(self.hostbox[rank][p ^ 1], non_blocking=True)
         st = torch.cuda.current_stream().cuda_stream
         for (r, side), (_off, _cnt, flags) in self.host_sides.items():
             if r == rank:

@@ -290,6 +290,10 @@ int gmt_debug_set_push_delay(unsigned int max_ns);
  * `ns` nanoseconds and do nothing else -- for tests that a kernel of this library does not depend on
  * having the whole GPU (no counterpart in the reference). */
 int gmt_debug_occupy(int ctas, unsigned long long ns, gmt_stream_t stream);
+/* Test hook: single-rank (non-cooperative) collective launches use up to `factor` times more CTAs
+ * than can be resident at once (1 = off, the default).  A kernel that waited for a sibling CTA of its
+ * own grid would then expire its bounded spin; the collectives here wait for other ranks only. */
+int gmt_debug_set_grid_factor(int factor);
 /* flag words needed on `side` for the given interior extents */
 int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
 

@@ -212,7 +212,9 @@ def test_cli_gpu_fused_single_rank():
     tests = [ln for ln in lines if ln.startswith("TEST")]
     assert len(tests) == 12
     for ln in tests[:8]:
-        assert float(re.search(r"err=(\S+)", ln).group(1)) < 1e-6
+        # one spacing (8/64) for both coordinates like the reference: the other axis reaches 512, and
+        # err= is the rounding noise against y^2 ~ 2.6e5 (tests/test_cpu_units.py pins it to the oracle)
+        assert float(re.search(r"err=(\S+)", ln).group(1)) < 1e-4
     lines = run_cli("mpi_daxpy_nvtx", "--n-per-node", 1 << 20, "--managed", cpu=False)
     match_all(lines, [r"0/1 SUM = 524288\.500000", r"0/1 ALLSUM = 524288\.500000",
                       r"CUDA PreferredLocation of 'd_x' is (CPU|DEVICE|INVALID) \(-?\d+\)"])
