@@ -109,6 +109,42 @@ def stencils(rt, space, args):
             free()
 
 
+def exchanges(rt, space, args):
+    """The halo exchange ALONE -- the reference's timed quantity (mpi_stencil_gt.cc:200-204,
+    mpi_stencil2d_gt.cc:512-522) -- peer-memory kernel vs the library restatement (pack kernels, NCCL
+    send/recv, unpack kernels, device-wide syncs), for the message sizes the reference programs use:
+    16 B (1-D), 128 KiB strided (mpi_stencil2d_sycl_oo default), 1 MiB strided, 8 MiB strided (dim 0),
+    8 MiB contiguous (dim 1), and the flagship's four 256 KiB faces."""
+    W, dev, r = rt.world_size, rt.device, rt.rank
+    cases = [("1d_16B", "1d", 1 << 22, 0), ("dim0_128KiB_strided", "dim0", 1024, 8192),
+             ("dim0_1MiB_strided", "dim0", 1024, 65536), ("dim0_8MiB_strided", "dim0", 1024, 524288),
+             ("dim1_8MiB_contiguous", "dim1", 524288, 1024), ("grid_4x256KiB", "grid", 16384, 16384)]
+    if args.quick:
+        cases = cases[:3]
+    for label, mode, nx, ny in cases:
+        for impl in ("fused", "baseline"):
+            if mode == "1d":
+                wl = Stencil1DWorkload(rt, nx, impl=impl, with_err=False, space=space if impl == "fused" else None)
+                fn = wl.exchange_only
+            else:
+                wl = Stencil2DWorkload(rt, nx, ny, mode=mode, impl=impl, with_err=False,
+                                       space=space if impl == "fused" else None, stage="device")
+                fn = wl.exchange
+            wl.setup()
+            if impl == "fused":
+                ms, how = graph_ms(fn, 50, 5, dev)
+                eager = t_ms(fn, 50, 5, dev)
+                rec = {"us": ms * 1e3, "timing": how, "us_eager_python_call": eager * 1e3}
+                if mode != "1d":
+                    rec["halo_bytes_out_per_gpu"] = wl.plan.halo_bytes_out(r)
+            else:
+                rec = {"us": t_ms(fn, 30, 5, dev) * 1e3, "timing": "eager (device-wide syncs inside every call)"}
+            wl.check()
+            emit(rt, {"config": "halo_exchange_alone", "case": label, "impl": impl, "n_gpus": W, **rec})
+            del wl
+            free()
+
+
 def daxpy(rt, space, args):
     W, dev, r = rt.world_size, rt.device, rt.rank
     sizes = [1 << 20, (48 << 20) // W]
@@ -144,9 +180,13 @@ def collectives(rt, space, args):
     for sbytes in sizes:
         n = sbytes // 8
         iters = 200 if sbytes <= (1 << 16) else (50 if sbytes <= (1 << 22) else 10)
-        variants = [("fused_p2p", lambda: pc.allgather_inplace(n))]
+        variants = [("fused_p2p", lambda: pc.allgather_inplace(n, mode="p2p"))]
+        if n <= pc.ll_gather_max:
+            variants.append(("fused_ll", lambda: pc.allgather_inplace(n, mode="ll")))
         if pc.has_multicast:
-            variants.append(("fused_multicast", lambda: pc.allgather_inplace(n, multicast=True)))
+            variants.append(("fused_multicast", lambda: pc.allgather_inplace(n, mode="multimem")))
+            variants.append(("fused_multicast_weak", lambda: pc.allgather_inplace(n, mode="multimem_weak")))
+            variants.append(("fused_mc_plain_store", lambda: pc.allgather_inplace(n, mode="mc_store")))
         variants.append(("fused_gather_root0", lambda: pc.gather_inplace(n, 0)))
         variants.append(("nccl_allgather", lambda: dist.all_gather_into_tensor(ref[:n * W], ref[r * n:(r + 1) * n])))
         for name, fn in variants:
@@ -186,8 +226,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--max-slice", type=int, default=1 << 28, help="largest allgather slice in bytes")
-    ap.add_argument("--only", default="stencils,daxpy,collectives")
+    ap.add_argument("--max-slice", type=int, default=1 << 30, help="largest allgather slice in bytes (BASELINE config 5: 1 GiB)")
+    ap.add_argument("--only", default="stencils,exchanges,daxpy,collectives")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     rt = runtime.init()
@@ -199,6 +239,8 @@ def main():
     only = args.only.split(",")
     if "stencils" in only:
         stencils(rt, space, args)
+    if "exchanges" in only:
+        exchanges(rt, space, args)
     if "daxpy" in only:
         daxpy(rt, space, args)
     if "collectives" in only:

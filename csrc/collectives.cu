@@ -27,7 +27,7 @@ constexpr int kLLBase = 64;       // LL slots: [parity][src rank][2 words] after
 constexpr int64_t kLLMaxCells = 1LL << 18;  // n x world up to here: vectors travel as LL cells by default
 //   (same rule as parallel/collectives.py: each double costs 16 bytes per peer, so at 8 ranks the
 //   switch to one-/two-shot comes at 32 Ki doubles, at 2 ranks at 128 Ki)
-constexpr int64_t kLLGatherMax = 8192;      // allgather slices up to 64 KiB can travel as LL cells
+constexpr int64_t kLLGatherMax = 65536;     // allgather slices up to 512 KiB can travel as LL cells (given stage_cap)
 constexpr uint32_t kStatusTooBig = 0x1000u; // status word: the call needed more LL cells than stage_cap
 
 struct CollShared {
@@ -229,7 +229,7 @@ __device__ __forceinline__ uint64_t* ll_cell(const CollShared& S, int owner, int
          (((int64_t)par * S.R.world + src) * S.R.stage_cap + i) * 2;
 }
 
-// ---- small allgather through LL cells (slices up to 64 KiB).  The flag-based kernel above pays two
+// ---- small allgather through LL cells (slices up to 512 KiB when the staging area has the cells).  The flag-based kernel above pays two
 // signalling rounds (entry: nobody's user buffer may be written before its owner is in the call;
 // exit: my slice has landed everywhere) = two NVLink round trips plus two fences.  Here nobody
 // writes anybody's USER buffer: every value goes into the peers' LL cell area (staging memory that
@@ -624,7 +624,9 @@ __global__ void __launch_bounds__(32) barrier_kernel(const gmt_coll_rank* __rest
   uint64_t* mine = tab[r];
   const uint64_t e = ld_relaxed_sys(ep) + 1;
   if (t < W) {
-    st_release_sys(theirs + r, e);   // round 0, word [src]
+    // relaxed is enough: the barrier kernel itself wrote nothing, and the stream's earlier kernels
+    // completed (their stores performed at system scope) before this one started
+    st_relaxed_sys(theirs + r, e);   // round 0, word [src]
     if (!wait_flag_ge(mine + t, e, spin)) atomicExch(Rg->status, 1u + t);
   }
   __syncwarp();

@@ -170,23 +170,19 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
 // computing at once.  Chunks go out in the order the neighbour's tile loop will want them,
 // each followed by its own fence + flag, so the exchange streams underneath the sweep: the
 // export front moves ~10x faster than the compute front.
-// x-face chunks are exported in groups when there are many of them: the system-scope fence that
-// precedes a flag waits for the round trip of every store before it, so one fence per 1024-column
-// chunk (2 x 512 of them in the reference's dim-0 tile) kept each exporting CTA busy for ~4 us per
-// chunk; four chunks share one fence there.  Few chunks (the 16384^2 grid tile: 16 per side) keep
-// one fence each, so the first flags leave as early as possible.
-constexpr int kPushGroup = 4;
-constexpr int64_t kPushGroupMin = 64;  // group only when a side has at least this many chunks
-
+// x-face chunks can be exported in groups of `group` chunks per system fence ($GMT_PUSH_GROUP, dim-0
+// kernel).  Measured on 2 GPUs with the reference's dim-0 tile (2 x 512 chunks, tools/dim0_variants.py,
+// profiles/dim0_variants_n2.jsonl): 1 chunk per fence 1.302 ms, 4: 1.308, 8: 1.319, 15: 1.353 -- the
+// fences are NOT what the exchange costs there; later flags are.  The default stays one fence per chunk.
 template <int GX, int GY, bool kDebug, bool kNamedBar = false>
 __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i,
-                                           int max_push_ctas = 32)
+                                           int max_push_ctas = 32, int group = 0)
 {
   const int tid = threadIdx.x;
   const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
   const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
   const int64_t nfy = GY ? tiles_i : 0;
-  const int grp = nfx >= kPushGroupMin ? kPushGroup : 1;
+  const int grp = group > 0 ? group : 1;
   const int64_t ngx = (nfx + grp - 1) / grp;
   const int64_t nunits = 2 * (ngx + nfy);
   const int npush = min((int)gridDim.x, max_push_ctas);
@@ -387,16 +383,28 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
 // never execute a CTA barrier in the loop: each waits on the ring slot, sweeps its rows of the
 // tile and releases the slot, so a fast warp can run ahead of a slow one.
 constexpr int kWsDepth = 2;
+constexpr int kWsMaxTj = 64;   // widest dim-0 tile whose ghost pairs fit the shared-memory hand-over
 
-template <bool kErr, bool kDebug>
+// kLand = true : the communication warp copies the inbox into the array's own ghost cells (the array
+//                ends up as after the reference's boundary_exchange_x), the compute warps read them there;
+// kLand = false: the inbox IS the ghost storage: the communication warp hands the
+//                tile's ghost pairs over in shared memory and the two threads that own the face rows
+//                patch them into their registers.  No strided 16-byte writes into the array (each one
+//                a read-modify-write of a 32-byte sector under ECC), no re-read: `out` is identical,
+//                the array's ghost cells are NOT refreshed (call the exchange-only kernel for that).
+template <bool kErr, bool kDebug, bool kLand>
 __global__ void __launch_bounds__(kStThreads + 32, 2)
-  fused_dim0_ws_kernel(const gmt_halo2d_rank* __restrict__ ranks, int TJ)
+  fused_dim0_ws_kernel(const gmt_halo2d_rank* __restrict__ ranks, int tj_knobs)
 {
+  const int TJ = tj_knobs & 0xFFFF;
+  const int push_group = (tj_knobs >> 16) & 0xF;            // 0 = default rule
+  const int push_ctas = ((tj_knobs >> 20) & 0xFF) * 8;      // 0 = default (32)
   __shared__ gmt_halo2d_rank R;
   __shared__ double red[32];
   __shared__ int64_t ring[kWsDepth];
   __shared__ __align__(8) uint64_t full[kWsDepth];
   __shared__ __align__(8) uint64_t empty[kWsDepth];
+  __shared__ __align__(16) double2 ghost[kLand ? 1 : kWsDepth][2][kLand ? 1 : kWsMaxTj];
   load_rank(R, ranks + blockIdx.y);
   const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
   const int par = (int)(e & 1);
@@ -441,21 +449,29 @@ __global__ void __launch_bounds__(kStThreads + 32, 2)
           if (!wait_flag_ge(R.my_flag[lane] + j0 / kFlagCols, e, R.spin_limit)) atomicExch(R.status, 1u + lane);
         }
         __syncwarp();
-        for (int64_t j = j0 + lane; j < j1; j += 32) {
-          double* col = R.z + j * ldz;
-          if (sides & 1) stg128(col, ld_peer_f64x2(R.my_inbox[0][par] + 2 * j));
-          if (sides & 2) stg128(col + nx + 2, ld_peer_f64x2(R.my_inbox[1][par] + 2 * j));
+        if (kLand) {
+          for (int64_t j = j0 + lane; j < j1; j += 32) {
+            double* col = R.z + j * ldz;
+            if (sides & 1) stg128(col, ld_peer_f64x2(R.my_inbox[0][par] + 2 * j));
+            if (sides & 2) stg128(col + nx + 2, ld_peer_f64x2(R.my_inbox[1][par] + 2 * j));
+          }
+        } else {
+          // lanes 0-15 fetch the low face's pairs, lanes 16-31 the high face's
+          const int sd = lane >> 4;
+          if ((sides >> sd) & 1)
+            for (int64_t j = j0 + (lane & 15); j < j1; j += 16)
+              ghost[slot][sd][j - j0] = ld_peer_f64x2(R.my_inbox[sd][par] + 2 * j);
         }
         __syncwarp();
       }
       if (lane == 0) {
         ring[slot] = (int64_t)t;
-        mbar_arrive(&full[slot]);  // release: ring entry and landed ghosts are visible to the waiters
+        mbar_arrive(&full[slot]);  // release: ring entry and landed / handed-over ghosts are visible to the waiters
       }
     }
   } else {
     // ---------------- compute warps
-    push_faces<2, 0, kDebug, true>(R, e, par, tiles_i);
+    push_faces<2, 0, kDebug, true>(R, e, par, tiles_i, push_ctas > 0 ? push_ctas : 32, push_group);
     Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
     for (int k = 0;; ++k) {
       const int slot = k % kWsDepth;
@@ -465,7 +481,13 @@ __global__ void __launch_bounds__(kStThreads + 32, 2)
       if (t < 0) break;
       const int64_t tj = t / tiles_i, ti = t - tj * tiles_i;
       const int64_t j0 = tj * TJ;
-      tile2d<2, 0, kErr>(S, ti * kTileI, j0, min(ny, j0 + (int64_t)TJ), tid, err);
+      if (kLand) {
+        tile2d<2, 0, kErr>(S, ti * kTileI, j0, min(ny, j0 + (int64_t)TJ), tid, err);
+      } else {
+        const double2* glo = (ti == 0 && R.has[0]) ? ghost[slot][0] : nullptr;
+        const double2* ghi = (ti == tiles_i - 1 && R.has[1]) ? ghost[slot][1] : nullptr;
+        tile2d_d0_inbox<kErr>(S, ti * kTileI, j0, min(ny, j0 + (int64_t)TJ), tid, err, glo, ghi);
+      }
       __syncwarp();
       if ((tid & 31) == 0) mbar_arrive(&empty[slot]);
     }
@@ -491,28 +513,56 @@ __global__ void __launch_bounds__(kStThreads + 32, 2)
 // Exchange-only calls and fused steps can be mixed freely on one plan (each advances the epoch).
 // Every CTA exports all of its share before it waits for anything, and waits only for another
 // rank's exports, so the kernel cannot block itself whatever part of the grid is resident.
+// 1-D: the two boundary values of a side travel as two 16-byte "LL" cells (p2p.cuh) that fill the
+// side's 32-byte inbox exactly: data and "arrived" come in one store -- no fence, no separate flag, the
+// receiver polls the cells themselves.  (The fused 1-D kernel keeps the plain-values + flag layout in
+// the same inbox; both ranks of a pair always run the same kind of call in the same epoch.)
 template <bool kDebug>
 __global__ void __launch_bounds__(64) halo_exchange1d_kernel(const gmt_halo1d_rank* __restrict__ ranks)
 {
   __shared__ gmt_halo1d_rank R;
   load_rank(R, ranks + blockIdx.y);
   const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const uint64_t e32 = e & 0xffffffffull;
   const int par = (int)(e & 1);
   const int tid = threadIdx.x;
   if (tid == 0 || tid == 32) {
     const int s = tid >> 5;  // 0: low neighbour, 1: high neighbour
     if (R.has[s]) {
-      stg128(R.peer_inbox[s][par], ldg128(s == 0 ? R.z + 2 : R.z + R.n));
-      fence_sys();
+      const double2 v = ldg128(s == 0 ? R.z + 2 : R.z + R.n);
+      uint64_t* out = reinterpret_cast<uint64_t*>(R.peer_inbox[s][par]);
       if (kDebug) debug_delay(e * 131 + blockIdx.y * 7 + s);
-      st_release_sys(R.peer_flag[s], e);
-      if (!wait_flag_ge(R.my_flag[s], e, R.spin_limit)) atomicExch(R.status, 1u + s);
-      stg128(s == 0 ? R.z : R.z + R.n + 2, ld_peer_f64x2(R.my_inbox[s][par]));
+      st_ll_cell(out, v.x, e32);
+      st_ll_cell(out + 2, v.y, e32);
+      const uint64_t* in = reinterpret_cast<const uint64_t*>(R.my_inbox[s][par]);
+      const int64_t limit = R.spin_limit > 0 ? R.spin_limit : kDefaultSpinLimit;
+      double2 g = {0.0, 0.0};
+      bool ok = false;
+      for (int64_t it = 0; it < limit; ++it) {
+        if (ld_ll_cell(in, e32, g.x) && ld_ll_cell(in + 2, e32, g.y)) {
+          ok = true;
+          break;
+        }
+        if (it > 64) __nanosleep(32);
+      }
+      if (!ok) atomicExch(R.status, 1u + s);
+      stg128(s == 0 ? R.z : R.z + R.n + 2, g);
     }
   }
-  finish_epoch(R.done, R.epoch, e, 2);
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    st_relaxed_sys(R.epoch, e);
+  }
 }
 
+// 2-D.  Phase A: every CTA exports its share of the live faces -- all loads in flight, then all
+// stores, ONE system fence per CTA, then the flags of everything it exported.  (The fused kernels flag
+// chunk by chunk so that the exchange streams under the sweep; here nothing runs underneath, and one
+// fence instead of one per chunk is what counts.)  Phase B: for its share of (side, chunk) units the CTA
+// waits for the neighbour's flag and copies the inbox into the array's ghost cells, four 16-byte
+// pieces per thread in flight.  Only live sides are enumerated, so all CTAs share the work even when
+// a rank has a single neighbour.
 template <int GX, int GY, bool kDebug>
 __global__ void __launch_bounds__(kStThreads, 2) halo_exchange2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
 {
@@ -523,39 +573,121 @@ __global__ void __launch_bounds__(kStThreads, 2) halo_exchange2d_kernel(const gm
   const int tid = threadIdx.x;
   const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
   const int64_t tiles_i = (nx + kTileI - 1) / kTileI;
-  push_faces<GX, GY, kDebug>(R, e, par, tiles_i, (int)gridDim.x);   // every CTA exports
-  // landing units: (side, chunk) pairs in the same enumeration as the flags
   const int64_t nfx = GX ? (ny + kFlagCols - 1) / kFlagCols : 0;
   const int64_t nfy = GY ? tiles_i : 0;
-  const int64_t nunits = 2 * (nfx + nfy);
-  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-    int side;
+  // live sides: out[] = sides I export to (a neighbour), in[] = sides I receive on (neighbour or host)
+  int out_side[4], in_side[4], n_out = 0, n_in = 0;
+#pragma unroll
+  for (int sd = 0; sd < 4; ++sd) {
+    if (sd < 2 ? !GX : !GY) continue;
+    if (R.has[sd] == 1) out_side[n_out++] = sd;
+    if (R.has[sd] != 0) in_side[n_in++] = sd;
+  }
+  auto chunks_of = [&](int sd) { return sd < 2 ? nfx : nfy; };
+  // units of a side list: side-major blocks, [0, chunks(side0)), then side1's, ...
+  auto decode = [&](const int* sides, int n_sides, int64_t u, int& sd, int64_t& c) {
+    for (int k = 0; k < n_sides; ++k) {
+      const int64_t nc = chunks_of(sides[k]);
+      if (u < nc) {
+        sd = sides[k];
+        c = u;
+        return;
+      }
+      u -= nc;
+    }
+    sd = -1;
+    c = 0;
+  };
+  int64_t total_out = 0, total_in = 0;
+  for (int k = 0; k < n_out; ++k) total_out += chunks_of(out_side[k]);
+  for (int k = 0; k < n_in; ++k) total_in += chunks_of(in_side[k]);
+
+  // ---------------- phase A: export
+  for (int64_t u = blockIdx.x; u < total_out; u += gridDim.x) {
+    int sd;
     int64_t c;
-    if (u < 2 * nfx) {
-      side = (int)(u & 1);
-      c = u >> 1;
-    } else {
-      side = 2 + (int)((u - 2 * nfx) & 1);
-      c = (u - 2 * nfx) >> 1;
-    }
-    if (!R.has[side]) continue;  // physical side without a host feed: ghosts stay as they are
-    if (tid == 0) {
-      if (!wait_flag_ge(R.my_flag[side] + c, e, R.spin_limit)) atomicExch(R.status, 1u + side);
-    }
-    __syncthreads();
-    const double* box = R.my_inbox[side][par];
-    if (side < 2) {
-      const int64_t j0 = c * kFlagCols, j1 = min(ny, j0 + (int64_t)kFlagCols);
-      double* dst = R.z + (side == 0 ? 0 : nx + 2) + GY * ldz;
-      for (int64_t j = j0 + tid; j < j1; j += kStThreads) stg128(dst + j * ldz, ld_peer_f64x2(box + 2 * j));
+    decode(out_side, n_out, u, sd, c);
+    double* box = R.peer_inbox[sd][par];
+    double2 v[4];
+    if (sd < 2) {
+      const int64_t j0 = c * kFlagCols;
+      const double* src = R.z + (sd == 0 ? 2 : nx) + GY * ldz;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) v[q] = ldg128(src + j * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) stg128(box + 2 * j, v[q]);
+      }
     } else {
       const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
-      double* dst = R.z + GX + (side == 2 ? 0 : ny + 2) * ldz;
+      const double* src = R.z + GX + (sd == 2 ? 2 : ny) * ldz;
 #pragma unroll
-      for (int r = 0; r < 2; ++r)
-        for (int64_t i = i0 + 2 * tid; i < i1; i += 2 * kStThreads)
-          stg128(dst + i + r * ldz, ld_peer_f64x2(box + r * nx + i));
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
+      }
     }
+  }
+  __syncthreads();
+  if (tid == 0 && (int64_t)blockIdx.x < total_out) {
+    fence_sys();   // one fence: every store of this CTA above is ordered before every flag below
+    for (int64_t u = blockIdx.x; u < total_out; u += gridDim.x) {
+      int sd;
+      int64_t c;
+      decode(out_side, n_out, u, sd, c);
+      if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
+      st_relaxed_sys(R.peer_flag[sd] + c, e);
+    }
+  }
+
+  // ---------------- phase B: land
+  for (int64_t u = blockIdx.x; u < total_in; u += gridDim.x) {
+    int sd;
+    int64_t c;
+    decode(in_side, n_in, u, sd, c);
+    if (tid == 0) {
+      if (!wait_flag_ge(R.my_flag[sd] + c, e, R.spin_limit)) atomicExch(R.status, 1u + sd);
+    }
+    __syncthreads();   // the acquire of thread 0 + this barrier order the plain loads below after the flag
+    const double* box = R.my_inbox[sd][par];
+    double2 v[4];
+    if (sd < 2) {
+      const int64_t j0 = c * kFlagCols;
+      double* dst = R.z + (sd == 0 ? 0 : nx + 2) + GY * ldz;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) v[q] = ld_peer_f64x2(box + 2 * j);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) stg128(dst + j * ldz, v[q]);
+      }
+    } else {
+      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
+      double* dst = R.z + GX + (sd == 2 ? 0 : ny + 2) * ldz;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) v[q] = ld_peer_f64x2(box + (q >> 1) * nx + i);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
+        if (i < i1) stg128(dst + i + (q >> 1) * ldz, v[q]);
+      }
+    }
+    __syncthreads();
   }
   finish_epoch(R.done, R.epoch, e, 2);
 }
@@ -610,9 +742,11 @@ int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64
 }
 
 int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
-                            int gx, int gy, int with_err, gmt_stream_t stream)
+                            int gx, int gy, int with_err_flags, gmt_stream_t stream)
 {
   using namespace gmt;
+  const int with_err = with_err_flags & 1;
+  const bool from_inbox = (with_err_flags & 2) != 0;   // dim-0 slabs: ghosts consumed straight from the inbox
   GMT_REQUIRE(ranks_dev && n_ranks >= 1 && nx > 0 && ny > 0, GMT_EINVAL, "gmt_fused_stencil2d_f64: bad argument");
   GMT_REQUIRE((gx == 0 || gx == 2) && (gy == 0 || gy == 2) && (gx || gy), GMT_EINVAL,
               "gmt_fused_stencil2d_f64: ghost widths must be 0 or 2 and not both 0");
@@ -634,8 +768,12 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
     k = GMT_PICK(2, 0);
     nt = tiles_i * ((ny + tj - 1) / tj);
   } else if (gx && !gy) {
-    k = dbg ? (with_err ? (const void*)fused_dim0_ws_kernel<true, true> : (const void*)fused_dim0_ws_kernel<false, true>)
-            : (with_err ? (const void*)fused_dim0_ws_kernel<true, false> : (const void*)fused_dim0_ws_kernel<false, false>);
+    if (from_inbox && tj <= kWsMaxTj)
+      k = dbg ? (with_err ? (const void*)fused_dim0_ws_kernel<true, true, false> : (const void*)fused_dim0_ws_kernel<false, true, false>)
+              : (with_err ? (const void*)fused_dim0_ws_kernel<true, false, false> : (const void*)fused_dim0_ws_kernel<false, false, false>);
+    else
+      k = dbg ? (with_err ? (const void*)fused_dim0_ws_kernel<true, true, true> : (const void*)fused_dim0_ws_kernel<false, true, true>)
+              : (with_err ? (const void*)fused_dim0_ws_kernel<true, false, true> : (const void*)fused_dim0_ws_kernel<false, false, true>);
     threads = kStThreads + 32;
     nt = tiles_i * ((ny + tj - 1) / tj);
   } else if (!gx && gy) {
@@ -651,7 +789,14 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   // memory order by default (GMT_FUSED_ORDER=interior moves them to the end as well)
   const char* ord = getenv("GMT_FUSED_ORDER");
   const bool ws = gx && !gy && !oneshot;
-  const int tj_flags = tj | ((!ws && !(ord && ord[0] == 'i')) ? (1 << 16) : 0);
+  int tj_flags = tj | ((!ws && !(ord && ord[0] == 'i')) ? (1 << 16) : 0);
+  if (ws) {   // tuning knobs of the dim-0 export (tools/dim0_variants.py): chunks per fence, exporting CTAs
+    const char* pg = getenv("GMT_PUSH_GROUP");
+    const char* pc = getenv("GMT_PUSH_CTAS");
+    const int g = pg ? atoi(pg) : 0, c = pc ? atoi(pc) : 0;
+    if (g >= 1 && g <= 15) tj_flags |= g << 16;
+    if (c >= 8 && c <= 2040) tj_flags |= (c / 8) << 20;
+  }
   return launch_fused(k, ranks_dev, n_ranks, nt, as_stream(stream), tj_flags, threads, oneshot);
 }
 

@@ -210,6 +210,65 @@ __device__ __forceinline__ void tile2d(const Sten2d& S, int64_t i0, int64_t j0, 
   }
 }
 
+// dim-0 tile whose x-face ghost pairs come from shared memory (filled from the neighbours' inbox by the
+// communication warp) instead of the array's own ghost cells: glo / ghi hold one pair per column of
+// the tile, or are NULL when the tile does not touch that face (or the face is a physical boundary,
+// whose analytic ghosts are in the array).  Only the thread that owns rows 0..3 (resp. nx-4..nx-1)
+// patches two of its eight loaded values; everything else is the plain tile.
+template <bool kErr>
+__device__ __forceinline__ void tile2d_d0_inbox(const Sten2d& S, int64_t i0, int64_t j0, int64_t j1, int tid,
+                                                double& err, const double2* glo, const double2* ghi)
+{
+  const int64_t i = i0 + 4 * tid;
+  if (i >= S.nx) return;
+  double ex0 = 0, ex1 = 0, ex2 = 0, ex3 = 0;
+  if (kErr) {
+    const double x = S.x0 + (double)i * S.dx;
+    ex0 = S.sx_an(x);
+    ex1 = S.sx_an(x + S.dx);
+    ex2 = S.sx_an(x + 2 * S.dx);
+    ex3 = S.sx_an(x + 3 * S.dx);
+  }
+  // 0: plain thread, 1: owns rows 0..3 (low ghosts), 2: owns rows nx-4..nx-1 (high ghosts), 3: both (nx == 4)
+  const int patch = ((glo != nullptr && i == 0) ? 1 : 0) | ((ghi != nullptr && i == S.nx - 4) ? 2 : 0);
+  for (int64_t j = j0; j < j1; j += kBatch) {
+    double4_t A[kBatch], B[kBatch];
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      if (j + u < j1) {
+        const double* c = S.z + i + (j + u) * S.ldz;
+        A[u] = ldg256(c);
+        B[u] = ldg256(c + 4);
+      }
+    }
+    if (patch) {   // two threads of the CTA at most
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        if (j + u < j1) {
+          if (patch & 1) {
+            const double2 g = glo[j + u - j0];
+            A[u].x = g.x;
+            A[u].y = g.y;
+          }
+          if (patch & 2) {
+            const double2 g = ghi[j + u - j0];
+            B[u].z = g.x;
+            B[u].w = g.y;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      if (j + u < j1) {
+        const double4_t o = sten_along(A[u], B[u], S.sx);
+        stg256(S.out + i + (j + u) * S.ldo, o);
+        if (kErr) err += (sq(o.x - ex0) + sq(o.y - ex1)) + (sq(o.z - ex2) + sq(o.w - ex3));
+      }
+    }
+  }
+}
+
 // grid size of a persistent kernel: SMs x occupancy, shared between n_ranks virtual ranks
 inline int persistent_grid(const void* kernel, int threads, int64_t ntiles, int n_ranks, int* out_grid)
 {

@@ -25,6 +25,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "p2p.cuh"
 #include "tma.cuh"
 
 namespace gmt {
@@ -117,6 +118,146 @@ __global__ void __launch_bounds__(kTmaConsumers + 32)
     }
     __syncwarp();
     if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+  }
+}
+
+// ===================================================================== 1-D, fused halo exchange
+// The TMA pipeline above with the halo exchange of gmt_fused_stencil1d_f64 folded in (replaces
+// boundary_exchange + stencil1d_5, mpi_stencil_gt.cc:83-122,206): the producer thread of CTA 0 stores
+// the rank's two boundary values per side into the neighbours' inboxes and flags them; every
+// producer draws tiles interior-first, and the one that draws an edge tile first waits for the
+// neighbour's flag, puts the two ghost values into the array, makes them visible to the async proxy
+// (fence.proxy.async) and only then issues the bulk copy of that window.  The consumer warps never
+// see any of it.  Same descriptors, inboxes, flags and epoch as the LSU kernel (calls can be mixed).
+__global__ void __launch_bounds__(kTmaConsumers + 32)
+  fused1d_tma_kernel(const gmt_halo1d_rank* __restrict__ ranks)
+{
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kTmaStages;
+  int64_t* tile_of = reinterpret_cast<int64_t*>(smem + 128);
+  unsigned char* data = smem + 256;
+  __shared__ gmt_halo1d_rank R;
+  const int tid = threadIdx.x;
+  {
+    const uint64_t* src = reinterpret_cast<const uint64_t*>(ranks + blockIdx.y);
+    uint64_t* dst = reinterpret_cast<uint64_t*>(&R);
+    for (int w = tid; w < (int)(sizeof(gmt_halo1d_rank) / 8); w += blockDim.x) dst[w] = src[w];
+  }
+  if (tid == 0) {
+    for (int s = 0; s < kTmaStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kTmaConsumers / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  const int par = (int)(e & 1);
+  const int64_t n = R.n;
+  const double* __restrict__ in = R.z;
+  double* __restrict__ out = R.out;
+  const double scale = R.scale;
+  const int64_t ntiles = (n + kTmaTile - 1) / kTmaTile;
+  const int64_t first_int = R.has[0] ? 1 : 0;
+  const int64_t end_int = max(first_int, ntiles - (R.has[1] ? 1 : 0));
+  const int64_t n_int = end_int - first_int;
+
+  if (tid >= kTmaConsumers) {
+    if (tid == kTmaConsumers) {
+      if (blockIdx.x == 0) {   // export: 16 bytes per side, one fence, two flags
+        bool any = false;
+        for (int s = 0; s < 2; ++s)
+          if (R.has[s]) {
+            stg128(R.peer_inbox[s][par], ldg128(s == 0 ? R.z + 2 : R.z + n));
+            any = true;
+          }
+        if (any) fence_sys();
+        for (int s = 0; s < 2; ++s)
+          if (R.has[s]) st_relaxed_sys(R.peer_flag[s], e);
+      }
+      uint32_t* counter = R.done + 1;
+      for (int k = 0;; ++k) {
+        const int64_t c = (int64_t)atomicAdd(counter, 1u);
+        const int s = k % kTmaStages;
+        const uint32_t ph = (k / kTmaStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        if (c >= ntiles) {
+          tile_of[s] = -1;  // sentinel: consumers leave
+          mbar_arrive(&full[s]);
+          break;
+        }
+        // interior tiles first (they depend on nobody), then the edge tiles in index order
+        int64_t t;
+        if (c < n_int) {
+          t = first_int + c;
+        } else {
+          const int64_t q = c - n_int;
+          t = q < first_int ? q : end_int + (q - first_int);
+        }
+        const bool lo = (t == 0 && R.has[0]), hi = (t == ntiles - 1 && R.has[1]);
+        if (lo || hi) {
+          for (int sd = 0; sd < 2; ++sd) {
+            if (!(sd == 0 ? lo : hi)) continue;
+            if (!wait_flag_ge(R.my_flag[sd], e, R.spin_limit)) atomicExch(R.status, 1u + sd);
+            stg128(sd == 0 ? R.z : R.z + n + 2, ld_peer_f64x2(R.my_inbox[sd][par]));
+          }
+          __threadfence();
+          asm volatile("fence.proxy.async.global;" ::: "memory");  // my generic-proxy stores before the bulk copy's reads
+        }
+        tile_of[s] = t;
+        const int64_t t0 = t * kTmaTile;
+        const int64_t cnt = min((int64_t)kTmaTile, n - t0) + 4;
+        const uint32_t bytes = (uint32_t)(cnt * 8);
+        mbar_arrive_expect_tx(&full[s], bytes);
+        bulk_g2s(data + s * kTmaStageBytes, in + t0, bytes, &full[s]);
+      }
+    }
+  } else {
+    for (int k = 0;; ++k) {
+      const int s = k % kTmaStages;
+      const uint32_t ph = (k / kTmaStages) & 1;
+      mbar_wait(&full[s], ph);
+      const int64_t t = tile_of[s];
+      if (t < 0) break;
+      const int64_t t0 = t * kTmaTile;
+      const double* w = reinterpret_cast<const double*>(data + s * kTmaStageBytes);
+#pragma unroll
+      for (int u = 0; u < kTmaTile / (kTmaConsumers * 4); ++u) {
+        const int idx = u * kTmaConsumers * 4 + 4 * tid;
+        const int64_t i = t0 + idx;
+        if (i + 3 < n) {
+          const double2 a0 = *reinterpret_cast<const double2*>(w + idx);
+          const double2 a1 = *reinterpret_cast<const double2*>(w + idx + 2);
+          const double2 b0 = *reinterpret_cast<const double2*>(w + idx + 4);
+          const double2 b1 = *reinterpret_cast<const double2*>(w + idx + 6);
+          double4_t o;
+          o.x = sten5(a0.x, a0.y, a1.y, b0.x) * scale;
+          o.y = sten5(a0.y, a1.x, b0.x, b0.y) * scale;
+          o.z = sten5(a1.x, a1.y, b0.y, b1.x) * scale;
+          o.w = sten5(a1.y, b0.x, b1.x, b1.y) * scale;
+          stg256(out + i, o);
+        } else if (i < n) {
+          for (int64_t q = i; q < n; ++q) {
+            const int r = (int)(q - t0);
+            out[q] = sten5(w[r], w[r + 1], w[r + 3], w[r + 4]) * scale;
+          }
+        }
+      }
+      __syncwarp();
+      if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+    }
+  }
+  // last CTA of this rank: reset the counters and advance the epoch
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(R.done, 1u) == gridDim.x - 1) {
+      R.done[0] = 0u;
+      R.done[1] = 0u;
+      __threadfence();
+      st_relaxed_sys(R.epoch, e);
+    }
   }
 }
 
@@ -352,6 +493,36 @@ int gmt_stencil1d_tma_f64(int64_t n, const double* in, double* out, double scale
   const int grid = (int)std::min<int64_t>(ntiles, (int64_t)sm_count() * occ);
   stencil1d_tma_kernel<<<grid, kTmaConsumers + 32, kTmaSmemBytes, as_stream(stream)>>>(n, in, out, scale, counters);
   GMT_LAUNCH_CHECK();
+  return 0;
+}
+
+int gmt_fused_stencil1d_tma_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, gmt_stream_t stream)
+{
+  using namespace gmt;
+  GMT_REQUIRE(ranks_dev && n_ranks >= 1 && n > 0, GMT_EINVAL, "gmt_fused_stencil1d_tma_f64: bad argument");
+  GMT_REQUIRE(n % 2 == 0, GMT_EUNSUPPORTED, "gmt_fused_stencil1d_tma_f64: n must be even (16-byte halo stores, bulk copies)");
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  GMT_CUDA(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    GMT_CUDA(cudaFuncSetAttribute(fused1d_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes));
+    configured_dev = dev;
+  }
+  int occ = 0;
+  GMT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused1d_tma_kernel, kTmaConsumers + 32, kTmaSmemBytes));
+  if (occ < 1) occ = 1;
+  int64_t cap = (int64_t)sm_count() * occ;
+  if (n_ranks > 1) cap /= n_ranks;
+  GMT_REQUIRE(cap >= 1, GMT_ETOOBIG, "too many virtual ranks (%d) for one cooperative launch", n_ranks);
+  const int64_t ntiles = (n + kTmaTile - 1) / kTmaTile;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ntiles, cap));
+  void* args[] = {(void*)&ranks_dev};
+  if (n_ranks > 1)
+    GMT_CUDA(cudaLaunchCooperativeKernel((const void*)fused1d_tma_kernel, dim3(grid, n_ranks), dim3(kTmaConsumers + 32),
+                                         args, kTmaSmemBytes, as_stream(stream)));
+  else
+    GMT_CUDA(cudaLaunchKernel((const void*)fused1d_tma_kernel, dim3(grid, 1), dim3(kTmaConsumers + 32), args,
+                              kTmaSmemBytes, as_stream(stream)));
   return 0;
 }
 

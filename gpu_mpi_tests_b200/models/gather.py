@@ -34,7 +34,9 @@ class GatherWorkload:
                 raise RuntimeError("impl='fused' needs CUDA")
             self.space = space if space is not None else make_space(self.rt)
             self.world, self.ranks = self.space.world, list(self.space.ranks_here)
-            self.coll = PeerCollectives(self.space, buf_doubles=self.n * self.world, spin_limit=spin_limit)
+            # slices up to 512 KiB travel as LL cells: give the staging area that many cells per source rank
+            self.coll = PeerCollectives(self.space, buf_doubles=self.n * self.world, spin_limit=spin_limit,
+                                        stage_cap=min(max(self.n, 8192), 65536))
             self.allx = {r: self.coll.buffer(r) for r in self.ranks}
         else:
             self.space, self.coll = None, None

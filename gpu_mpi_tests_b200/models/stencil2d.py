@@ -31,7 +31,7 @@ class Stencil2DWorkload:
     def __init__(self, rt: "_rt.Runtime | None" = None, nx: int = 16384, ny: int = 16384, mode: str = "grid",
                  impl: str = "fused", with_err: bool = True, space: PeerSpace | None = None,
                  grid: tuple | None = None, stage: str = "none", mem_space: str = "device",
-                 spin_limit: int = 0, host_fed: bool = False):
+                 spin_limit: int = 0, host_fed: bool = False, land_ghosts: bool = True):
         """mode: 'grid' (gx=gy=2, px x py ranks), 'dim0' (gx=2, world x 1), 'dim1' (gy=2, 1 x world).
         nx, ny: per-rank interior extents (weak scaling)."""
         self.rt = rt or _rt.current()
@@ -65,7 +65,7 @@ class Stencil2DWorkload:
             self.space = space if space is not None else make_space(self.rt)
             self.plan = FusedStencil2D(self.space, self.px, self.py, nx, ny, self.gx, self.gy, with_err=with_err,
                                        spin_limit=spin_limit, mem_space=mem_space, host_fed=host_fed,
-                                       dx=dx, dy=dy)
+                                       dx=dx, dy=dy, land_ghosts=land_ghosts)
             self.ranks = self.plan.ranks
             self.z, self.out = self.plan.z, self.plan.out
             self.dx, self.dy, self.sx, self.sy = self.plan.dx, self.plan.dy, self.plan.sx, self.plan.sy

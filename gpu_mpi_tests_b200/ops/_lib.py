@@ -132,6 +132,7 @@ _SIGS = {
                                       c_ptr, c_i64, C.c_int, c_dbl, c_dbl, C.c_int, c_dbl, c_ptr]),
     "gmt_fused_stencil1d_f64": (None, [c_ptr, C.c_int, c_i64, C.c_int, c_ptr]),
     "gmt_fused_stencil2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, C.c_int, c_ptr]),
+    "gmt_fused_stencil1d_tma_f64": (None, [c_ptr, C.c_int, c_i64, c_ptr]),
     "gmt_halo_exchange1d_f64": (None, [c_ptr, C.c_int, c_ptr]),
     "gmt_halo_exchange2d_f64": (None, [c_ptr, C.c_int, c_i64, c_i64, C.c_int, C.c_int, c_ptr]),
     "gmt_halo2d_flag_count": (c_i64, [C.c_int, c_i64, c_i64]),

@@ -71,8 +71,15 @@ class FusedStencil1D(_PlanBase):
     """1-D slab-decomposed array y = x^3 on [0, 8) and its fused derivative step."""
 
     def __init__(self, space: PeerSpace, n_local: int, with_err: bool = True, spin_limit: int = 0,
-                 n_global: int | None = None):
+                 n_global: int | None = None, variant: str = "vector"):
+        """variant: "vector" (256-bit LSU loads, the default and the faster one) or "tma" (windows
+        streamed into shared memory by cp.async.bulk + mbarriers; no in-kernel error norm)."""
         super().__init__(space, with_err, spin_limit)
+        if variant not in ("vector", "tma"):
+            raise ValueError("variant must be vector or tma")
+        if variant == "tma" and with_err:
+            raise ValueError("the TMA variant has no in-kernel error norm: with_err=False")
+        self.variant = variant
         if n_local % 2:
             raise ValueError("fused 1-D exchange needs an even n_local (16-byte halo stores)")
         W = space.world
@@ -117,8 +124,11 @@ class FusedStencil1D(_PlanBase):
             local.init_stencil1d(self.z[r], None, self.n, r * self.n * self.dx, self.dx, r == 0, r == W - 1)
 
     def step(self) -> None:
-        lib.gmt_fused_stencil1d_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.n, int(self.with_err),
-                                    torch.cuda.current_stream().cuda_stream)
+        st = torch.cuda.current_stream().cuda_stream
+        if self.variant == "tma":
+            lib.gmt_fused_stencil1d_tma_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.n, st)
+        else:
+            lib.gmt_fused_stencil1d_f64(self._ranks_dev.data_ptr(), len(self.ranks), self.n, int(self.with_err), st)
         self.steps += 1
 
     def exchange(self) -> None:
@@ -144,8 +154,11 @@ class FusedStencil2D(_PlanBase):
     def __init__(self, space: PeerSpace, px: int, py: int, nx: int, ny: int, gx: int = 2, gy: int = 2,
                  with_err: bool = True, spin_limit: int = 0, dx: float | None = None, dy: float | None = None,
                  wx: float = 1.0, wy: float = 1.0, mem_space: str = "device", host_fed: bool = False,
-                 periodic: bool = False):
+                 periodic: bool = False, land_ghosts: bool = True):
         super().__init__(space, with_err, spin_limit)
+        # land_ghosts=False (dim-0 slabs only): step() consumes the x-face ghost values straight from
+        # the inbox and leaves z's own ghost cells alone -- same `out`, no strided writes into the array
+        self.land_ghosts = bool(land_ghosts) or not (gx and not gy)
         if periodic and with_err:
             raise ValueError("periodic grids have no analytic error norm (x^3 + y^2 does not wrap): with_err=False")
         if px * py != space.world:
@@ -266,7 +279,8 @@ class FusedStencil2D(_PlanBase):
         word of this step goes straight into that pinned host word instead of device memory."""
         desc = self._ranks_dev if result_slot is None else self._ranks_dev_slot[result_slot]
         lib.gmt_fused_stencil2d_f64(desc.data_ptr(), len(self.ranks), self.nx, self.ny, self.gx, self.gy,
-                                    int(self.with_err), torch.cuda.current_stream().cuda_stream)
+                                    int(self.with_err) | (0 if self.land_ghosts else 2),
+                                    torch.cuda.current_stream().cuda_stream)
         self.steps += 1
 
     def host_result_slots(self) -> list:

@@ -230,6 +230,11 @@ typedef struct {
 /* replaces boundary_exchange + stencil1d_5 (mpi_stencil_gt.cc:83-122,206) */
 int gmt_fused_stencil1d_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, int with_err,
                             gmt_stream_t stream);
+/* The same step with the data path of gmt_stencil1d_tma_f64: windows streamed into a shared-memory
+ * ring by cp.async.bulk (SASS UBLKCP) + mbarrier transaction counts; the producer thread also does the
+ * halo export, the flag waits and the ghost landing (followed by fence.proxy.async before the bulk
+ * copy that reads them).  No error norm.  Same descriptors / epoch: calls can be mixed. */
+int gmt_fused_stencil1d_tma_f64(const gmt_halo1d_rank* ranks_dev, int n_ranks, int64_t n, gmt_stream_t stream);
 /* The exchange alone -- boundary_exchange as a callable (mpi_stencil_gt.cc:83-122) and the
  * quantity the reference times (:200-204): store my two boundary values into each neighbour's
  * inbox, wait for theirs, put them into z's ghost cells.  Same descriptors, inboxes, flags and
@@ -268,6 +273,10 @@ typedef struct {
   int64_t spin_limit;
 } gmt_halo2d_rank;
 
+/* with_err: bit 0 = compute the error norm into err_sumsq; bit 1 (dim-0 slabs, gx == 2 && gy == 0,
+ * only) = take the x-face ghost values straight from the inbox: `out` is the same, but z's own ghost
+ * cells are NOT refreshed (no strided 16-byte writes into the array); call gmt_halo_exchange2d_f64
+ * when the array itself must hold them. */
 int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64_t nx, int64_t ny,
                             int gx, int gy, int with_err, gmt_stream_t stream);
 /* The exchange alone -- boundary_exchange_x / _y as a callable (mpi_stencil2d_gt.cc:136-373) and
@@ -308,7 +317,7 @@ int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
  * area that is double-buffered by epoch parity, so a rank that is one call ahead cannot disturb a
  * slower one.  Small payloads skip the flags altogether: they travel as 16-byte "LL" cells in the
  * staging area whose two 8-byte words each carry 32 payload bits and the 32-bit epoch, so data and
- * "arrived" come in one store (LL all-reduce, allgather of slices up to 64 KiB, and the per-CTA
+ * "arrived" come in one store (LL all-reduce, allgather of slices up to 512 KiB, and the per-CTA
  * partial sums of gmt_daxpy_allreduce_f64).
  *
  * Sizes: a staging area is gmt_coll_stage_bytes(world, stage_cap) bytes; stage_cap must be at least

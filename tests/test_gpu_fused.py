@@ -49,6 +49,41 @@ def test_fused_stencil1d(dev, world, n):
         assert close(plan.out[r], local.stencil1d(plan.z[r], plan.scale))
 
 
+@pytest.mark.parametrize("world,n", [(1, 4096), (2, 64), (3, 1000), (4, 8192), (8, 65536), (5, 4096 * 3 + 2), (2, 1 << 20)])
+def test_fused_stencil1d_tma_variant(dev, world, n):
+    """The fused 1-D step on the TMA data path (cp.async.bulk ring): same result as the LSU kernel,
+    ghosts landed, and the two variants can be mixed on one plan (same inboxes / flags / epoch)."""
+    plan = FusedStencil1D(VirtualSpace(world, dev), n, with_err=False, spin_limit=1 << 24, variant="tma")
+    plan.init_analytic()
+    for r in plan.ranks:
+        if r > 0:
+            plan.z[r][:2] = 1e30
+        if r < world - 1:
+            plan.z[r][-2:] = 1e30
+    for it in range(4):
+        for r in plan.ranks:
+            plan.z[r][2:-2].mul_(1.0 + 1e-4 * ((it + r) % 3))
+        plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [4] * world
+    for r in plan.ranks:
+        if r > 0:
+            assert torch.equal(plan.z[r][:2], plan.z[r - 1][-4:-2])
+        if r < world - 1:
+            assert torch.equal(plan.z[r][-2:], plan.z[r + 1][2:4])
+        assert close(plan.out[r], local.stencil1d(plan.z[r], plan.scale))
+    plan.variant = "vector"      # same plan, LSU kernel: the epoch and the inbox parities carry over
+    plan.step()
+    plan.variant = "tma"
+    plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [6] * world
+    for r in plan.ranks:
+        assert close(plan.out[r], local.stencil1d(plan.z[r], plan.scale))
+
+
 CASES_2D = [
     # px, py, nx, ny, gx, gy
     (1, 1, 2048, 512, 2, 2),
@@ -62,7 +97,7 @@ CASES_2D = [
     (3, 2, 36, 50, 2, 2),
     (3, 3, 1028, 300, 2, 2),     # the centre rank has FOUR live faces
     (3, 4, 2048, 130, 2, 2),     # two ranks with four live faces, several row tiles
-    (2, 1, 64, 66000, 2, 0),     # >= 64 x-face chunks: exported in groups of 4 per fence
+    (2, 1, 64, 66000, 2, 0),     # 65 x-face chunks per side
 ]
 
 
@@ -88,6 +123,43 @@ def test_fused_stencil2d(dev, px, py, nx, ny, gx, gy):
         else:
             ref = local.stencil2d(z, 1, plan.sy)
         assert close(plan.out[r], ref)
+
+
+@pytest.mark.parametrize("px,nx,ny", [(4, 1024, 256), (2, 4096, 100), (3, 64, 3000), (2, 64, 66000), (1, 1024, 64)])
+def test_fused_dim0_ghosts_straight_from_the_inbox(dev, px, nx, ny, monkeypatch):
+    """land_ghosts=False (dim-0 slabs): the inbox is the ghost storage.  Same `out` as the landing
+    flavour, z's own ghost cells stay untouched (still poisoned), and exchange() fills them on demand."""
+    if ny >= 60000:
+        monkeypatch.setenv("GMT_PUSH_GROUP", "4")     # the tuning knob: several chunks per fence
+        monkeypatch.setenv("GMT_PUSH_CTAS", "16")
+    plan = FusedStencil2D(VirtualSpace(px, dev), px, 1, nx, ny, 2, 0, with_err=True, spin_limit=1 << 24,
+                          land_ghosts=False)
+    ref = FusedStencil2D(VirtualSpace(px, dev), px, 1, nx, ny, 2, 0, with_err=True, spin_limit=1 << 24)
+    assert not plan.land_ghosts and ref.land_ghosts
+    plan.init_analytic(poison=1e30)
+    ref.init_analytic(poison=1e30)
+    for it in range(4):
+        for r in plan.ranks:     # the field changes every step: both inbox parities carry fresh values
+            plan.z[r][:, 2:-2].mul_(1.0 + 1e-3 * (it + r))
+            ref.z[r][:, 2:-2].mul_(1.0 + 1e-3 * (it + r))
+        plan.step()
+        ref.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    ref.check_status()
+    for r in plan.ranks:
+        assert close(plan.out[r], ref.out[r]), f"rank {r}"            # same arithmetic on the same values
+        assert float((plan.out[r] - ref.out[r]).abs().max()) < 1e20    # no poisoned ghost leaked into a result
+        assert plan.err_norm(r) == pytest.approx(ref.err_norm(r), rel=1e-3, abs=1e-9)
+        if r > 0:
+            assert float(plan.z[r][:, :2].min()) == 1e30              # not landed
+        if r < px - 1:
+            assert float(plan.z[r][:, -2:].min()) == 1e30
+    plan.exchange()
+    torch.cuda.synchronize()
+    plan.check_status()
+    for r in plan.ranks:
+        assert torch.equal(plan.z[r], ref.z[r])
 
 
 def _ghost_pairs(plan, r):

@@ -46,9 +46,13 @@ def test_stress_2d_grid_with_injected_delays(dev, delays):
     assert plan.epochs() == [steps] * (px * py)
 
 
+@pytest.mark.parametrize("land", [True, False])
 @pytest.mark.parametrize("gx,gy,px,py,nx,ny", [(2, 0, 4, 1, 1024, 4096), (0, 2, 1, 4, 4096, 512)])
-def test_stress_2d_slabs_with_injected_delays(dev, delays, gx, gy, px, py, nx, ny):
-    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, gx, gy, with_err=True, spin_limit=1 << 26)
+def test_stress_2d_slabs_with_injected_delays(dev, delays, gx, gy, px, py, nx, ny, land):
+    if not land and gy:
+        pytest.skip("land_ghosts=False exists for dim-0 slabs only")
+    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, gx, gy, with_err=True, spin_limit=1 << 26,
+                          land_ghosts=land)
     plan.init_analytic(poison=1e30)
     for _ in range(60):
         plan.step()
@@ -56,6 +60,37 @@ def test_stress_2d_slabs_with_injected_delays(dev, delays, gx, gy, px, py, nx, n
     plan.check_status()
     for r in plan.ranks:
         assert float((plan.out[r] - plan.analytic(r)).abs().max()) < 1e-6
+
+
+def test_stress_four_live_faces_and_exchange_only_with_injected_delays(dev, delays):
+    """3 x 3 grid: the centre rank has four live faces.  Fused steps and exchange-only calls are mixed
+    on the same plan with delayed flags, the field changing before every call."""
+    px = py = 3
+    nx, ny = 1028, 300
+    plan = FusedStencil2D(VirtualSpace(px * py, dev), px, py, nx, ny, 2, 2, with_err=False, spin_limit=1 << 26)
+    plan.init_analytic(poison=1e30)
+    calls = 60
+    for it in range(calls):
+        for r in plan.ranks:
+            plan.z[r][2:-2, 2:-2].mul_(1.0 + 1e-3 * ((it + r) % 5))
+        if it % 3 == 1:
+            plan.exchange()
+        else:
+            plan.step()
+    torch.cuda.synchronize()
+    plan.check_status()
+    assert plan.epochs() == [calls] * (px * py)
+    c = plan.grids[4]
+    assert all(c.neighbour(s) >= 0 for s in range(4))
+    for r in plan.ranks:
+        g, z = plan.grids[r], plan.z[r]
+        for side, (mine, theirs) in {0: (z[2:-2, :2], lambda o: o[2:-2, -4:-2]), 1: (z[2:-2, -2:], lambda o: o[2:-2, 2:4]),
+                                     2: (z[:2, 2:-2], lambda o: o[-4:-2, 2:-2]), 3: (z[-2:, 2:-2], lambda o: o[2:4, 2:-2])}.items():
+            nb = g.neighbour(side)
+            if nb >= 0:
+                assert torch.equal(mine, theirs(plan.z[nb])), f"rank {r} side {side}"
+        ref = local.stencil2d_xy(z, plan.sx, plan.sy)
+        assert float((plan.out[r] - ref).abs().max()) <= 1e-10 * (float(ref.abs().max()) + 1.0)
 
 
 def test_stress_1d_with_injected_delays(dev, delays):
