@@ -175,7 +175,7 @@ def collectives(rt, space, args):
     sizes = [1 << k for k in range(10, 31, 2)]
     sizes = [s for s in sizes if s <= args.max_slice]
     nmax = max(sizes) // 8
-    pc = PeerCollectives(space, buf_doubles=nmax * W)
+    pc = PeerCollectives(space, buf_doubles=nmax * W, stage_cap=65536)   # LL cells for slices up to 512 KiB
     ref = torch.empty(nmax * W, dtype=F64, device=dev)
     for sbytes in sizes:
         n = sbytes // 8

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused1d_kernel(const gmt_halo1d
 // profiles/dim0_variants_n2.jsonl): 1 chunk per fence 1.302 ms, 4: 1.308, 8: 1.319, 15: 1.353 -- the
 // fences are NOT what the exchange costs there; later flags are.  The default stays one fence per chunk.
 template <int GX, int GY, bool kDebug, bool kNamedBar = false>
-__device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i,
+__device__ __noinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, int par, int64_t tiles_i,
                                            int max_push_ctas = 32, int group = 0)
 {
   const int tid = threadIdx.x;
@@ -187,61 +187,123 @@ __device__ __forceinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e,
   const int64_t nunits = 2 * (ngx + nfy);
   const int npush = min((int)gridDim.x, max_push_ctas);
   if ((int)blockIdx.x >= npush) return;
-  for (int64_t u = blockIdx.x; u < nunits; u += npush) {
-    int side;
-    int64_t c, c_end;
+  auto cta_bar = [&]() {
+    if (kNamedBar)
+      asm volatile("bar.sync 1, %0;" ::"n"(kStThreads) : "memory");  // the 256 exporting threads only
+    else
+      __syncthreads();
+  };
+  // unit u -> (side, first chunk); units of the two sides of a direction alternate
+  auto decode = [&](int64_t u, int& side, int64_t& c) {
     if (u < 2 * ngx) {
       side = (int)(u & 1);
       c = (u >> 1) * grp;
-      c_end = min(nfx, c + grp);
     } else {
       side = 2 + (int)((u - 2 * ngx) & 1);
       c = (u - 2 * ngx) >> 1;
-      c_end = c + 1;
     }
-    if (R.has[side] != 1) continue;  // CTA-uniform; 2 = fed by the host, nothing to export
-    double* box = R.peer_inbox[side][par];
+  };
+  // this CTA's next unit at or after u whose side has a neighbour (has == 2: fed by the host, nothing to export)
+  auto next_live = [&](int64_t u) {
+    for (; u < nunits; u += npush) {
+      int side;
+      int64_t c;
+      decode(u, side, c);
+      if (R.has[side] == 1) break;
+    }
+    return u;
+  };
+  // one chunk = four 16-byte pieces per thread: an x-face chunk is kFlagCols columns x 2 rows (strided
+  // pieces gathered into a contiguous inbox), a y-face chunk kTileI rows x 2 columns
+  auto load_chunk = [&](int side, int64_t c, double2* v) {
     if (side < 2) {
       const double* src = R.z + (side == 0 ? 2 : nx) + GY * ldz;
-#pragma unroll 1
-      for (int64_t cc = c; cc < c_end; ++cc) {
-        const int64_t j0 = cc * kFlagCols;
-        double2 v[kFlagCols / kStThreads];
+      const int64_t j0 = c * kFlagCols;
 #pragma unroll
-        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-          const int64_t j = j0 + tid + q * kStThreads;
-          if (j < ny) v[q] = ldg128(src + j * ldz);
-        }
-#pragma unroll
-        for (int q = 0; q < kFlagCols / kStThreads; ++q) {
-          const int64_t j = j0 + tid + q * kStThreads;
-          if (j < ny) stg128(box + 2 * j, v[q]);
-        }
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) v[q] = ldg128(src + j * ldz);
       }
     } else {
       const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
       const double* src = R.z + GX + (side == 2 ? 2 : ny) * ldz;
-      double2 v[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
         if (i < i1) v[q] = ldg128(src + i + (q >> 1) * ldz);
       }
+    }
+  };
+  auto store_chunk = [&](int side, int64_t c, const double2* v) {
+    double* box = R.peer_inbox[side][par];
+    if (side < 2) {
+      const int64_t j0 = c * kFlagCols;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t j = j0 + tid + q * kStThreads;
+        if (j < ny) stg128(box + 2 * j, v[q]);
+      }
+    } else {
+      const int64_t i0 = c * kTileI, i1 = min(nx, i0 + (int64_t)kTileI);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int64_t i = i0 + 2 * tid + (q & 1) * 2 * kStThreads;
         if (i < i1) stg128(box + (q >> 1) * nx + i, v[q]);
       }
     }
-    if (kNamedBar)
-      asm volatile("bar.sync 1, %0;" ::"n"(kStThreads) : "memory");  // the 256 exporting threads only
-    else
-      __syncthreads();
+  };
+  static_assert(kFlagCols == 4 * kStThreads && kTileI == 4 * kStThreads, "a chunk is four pieces per thread");
+
+  if (grp == 1) {
+    // software pipeline: the loads of the NEXT chunk are issued before the fence of this one, so their
+    // latency runs concurrently with the round trip the fence waits for -- and no flag is delayed
+    double2 cur[4], nxt[4];
+    int64_t u = next_live(blockIdx.x);
+    int side = 0;
+    int64_t c = 0;
+    if (u < nunits) {
+      decode(u, side, c);
+      load_chunk(side, c, cur);
+    }
+    while (u < nunits) {
+      store_chunk(side, c, cur);
+      const int64_t u2 = next_live(u + npush);
+      int side2 = 0;
+      int64_t c2 = 0;
+      if (u2 < nunits) {
+        decode(u2, side2, c2);
+        load_chunk(side2, c2, nxt);
+      }
+      cta_bar();
+      if (tid == 0) {
+        fence_sys();
+        if (kDebug) debug_delay(e * 8191 + (uint64_t)u * 31 + blockIdx.y);
+        st_relaxed_sys(R.peer_flag[side] + c, e);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
+      u = u2, side = side2, c = c2;
+    }
+    return;
+  }
+  // several x-face chunks per fence (tuning knob only)
+  for (int64_t u = next_live(blockIdx.x); u < nunits; u = next_live(u + npush)) {
+    int side;
+    int64_t c;
+    decode(u, side, c);
+    const int64_t c_end = side < 2 ? min(nfx, c + grp) : c + 1;
+#pragma unroll 1
+    for (int64_t cc = c; cc < c_end; ++cc) {
+      double2 v[4];
+      load_chunk(side, cc, v);
+      store_chunk(side, cc, v);
+    }
+    cta_bar();
     if (tid == 0) {
       fence_sys();
       for (int64_t cc = c; cc < c_end; ++cc) {
         if (kDebug) debug_delay(e * 8191 + (uint64_t)(u + cc) * 31 + blockIdx.y);
-        st_release_sys(R.peer_flag[side] + cc, e);
+        st_relaxed_sys(R.peer_flag[side] + cc, e);
       }
     }
   }

@@ -378,10 +378,10 @@ int gmt_gather_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int r
 int gmt_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, int algo, gmt_stream_t stream);
 /* fused daxpy + global sum: y <- a*in + y on each rank, every rank's *out <- sum over all ranks
  * of sum(y_new)  (cublasDaxpy + MPI_Allgather + host sums, mpi_daxpy_nvtx.cc:245-310, in one kernel).
- * One-shot grid in address order; every CTA stores its partial as an LL cell into every rank's
- * staging area and the last CTA of each rank adds all world x grid cells in a fixed order (same
- * bits on every rank, reproducible).  Needs stage_cap >= gmt_coll_min_stage_cap(); n must be the
- * same on every rank. */
+ * One-shot grid in address order; every CTA leaves its partial as an LL cell in its own rank's
+ * staging area, the last CTA adds them in a fixed order, and the rank totals cross NVLink as one LL
+ * cell per peer and are added in rank order (same bits on every rank, reproducible).  Needs
+ * stage_cap >= gmt_coll_min_stage_cap(); n must be the same on every rank. */
 int gmt_daxpy_allreduce_f64(const gmt_coll_rank* ranks_dev, int n_ranks, int64_t n, double a,
                             gmt_stream_t stream);
 /* axis sum of the column-major (nx, ny, ld) array `in` whose epilogue all-reduces the first n_out

@@ -313,3 +313,52 @@ def test_native_mpi_daxpy_program():
     if n_dev > 1:
         res = subprocess.run([str(exe), "--ranks", str(n_dev + 1)], capture_output=True, text=True, timeout=60)
         assert res.returncode == 1 and "not a multiple of number of GPUs" in res.stdout
+
+
+def test_native_mpi_daxpy_gt_program():
+    """mpi_daxpy_gt's line (mpi_daxpy_gt.cc:92): r/N [dev:0x<packed PCI id>] SUM = 524800.000000, two ranks per GPU."""
+    exe = EXE.parent / "gmt_mpi_daxpy_gt"
+    n_dev = torch.cuda.device_count()
+    ranks = 2 * n_dev
+    res = subprocess.run([str(exe), "--ranks", str(ranks)], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout + res.stderr
+    lines = res.stdout.strip().splitlines()
+    assert len(lines) == ranks
+    for r, ln in enumerate(lines):
+        assert re.fullmatch(rf"{r}/{ranks} \[{r // 2}:0x[0-9a-f]{{8}}\] SUM = 524800\.000000", ln), ln
+
+
+@pytest.mark.parametrize("oo", [False, True])
+def test_native_stencil2d_sycl_programs(oo):
+    """The two SYCL programs' native counterpart: parameter block, per-rank exchange time (the exchange
+    alone, device-timed) and err_norm lines in each program's own format (mpi_stencil2d_sycl.cc:422-434,530,550;
+    mpi_stencil2d_sycl_oo.cc:575-581,679,700); two ranks (one GPU: both on it, cooperative launch)."""
+    exe = EXE.parent / "gmt_stencil2d_sycl"
+    F8 = r"\d+\.\d{8}"
+    if oo:
+        args = ["--oo", "2", "0", "6", "--ranks", "2"]
+    else:
+        args = ["512", "1", "6", "--ranks", "2", "--ny", "4096"]
+    res = subprocess.run([str(exe), *args], capture_output=True, text=True, timeout=180)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = res.stdout
+    assert "n procs    = 2" in out and "n_iter     = 6" in out and "n_warmup   = 5" in out
+    if oo:
+        assert "n_global   = 2048" in out and "n_local    = 1024" in out and "stage_host = 0" in out
+        for r in range(2):
+            assert re.search(rf"^{r}: exchange time {F8} ms$", out, re.M), out
+            m = re.search(rf"^{r}: \[0x[0-9a-f]{{8}}\] err_norm = ({F8})$", out, re.M)
+            assert m and float(m.group(1)) < 1e-3, out
+    else:
+        assert "ny         = 4096" in out and "nx_global  = 1024" in out and "nx_local   = 512" in out
+        assert "stage_host = 1" in out and re.search(r"^dev bytes  = \d+\.\d{3} (MB|GB)$", out, re.M)
+        for r in range(2):
+            assert re.search(rf"^{r} [0-9a-f]{{4}}:[0-9a-f]{{2}}:[0-9a-f]{{2}}\.0\([0-9a-f]{{16}}\)$", out, re.M), out
+            assert re.search(rf"^{r}/2 exchange time {F8} ms$", out, re.M), out
+            m = re.search(rf"^{r}/2 \[\d+:0x[0-9a-f]{{8}}\] err_norm = ({F8})$", out, re.M)
+            assert m and float(m.group(1)) < 1e-3, out
+    # divisor check of the square-domain form
+    if oo:
+        res = subprocess.run([str(exe), "--oo", "1", "0", "2", "--ranks", "3"], capture_output=True, text=True, timeout=60)
+        if torch.cuda.device_count() in (1, 3):
+            assert res.returncode == 1 and "must be divisor of domain size" in res.stdout
