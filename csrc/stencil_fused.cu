@@ -254,7 +254,7 @@ __device__ __noinline__ void push_faces(const gmt_halo2d_rank& R, uint64_t e, in
   };
   static_assert(kFlagCols == 4 * kStThreads && kTileI == 4 * kStThreads, "a chunk is four pieces per thread");
 
-  if (grp == 1) {
+  if (group == 0) {
     // software pipeline: the loads of the NEXT chunk are issued before the fence of this one, so their
     // latency runs concurrently with the round trip the fence waits for -- and no flag is delayed
     double2 cur[4], nxt[4];
@@ -327,6 +327,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
 {
   const int TJ = tj_flags & 0xFFFF;
   const bool natural = (tj_flags >> 16) & 1;   // x-face tiles in memory order (they wait in place)
+  const int push_group = (tj_flags >> 17) & 1 ? 1 : 0;   // 1: plain export loop (A/B knob), 0: pipelined
   __shared__ gmt_halo2d_rank R;
   __shared__ double red[32];
   __shared__ int64_t next_tile[2];
@@ -343,7 +344,7 @@ __global__ void __launch_bounds__(kStThreads, 2) fused2d_kernel(const gmt_halo2d
                                   GY && R.has[2], GY && R.has[3], natural);
   const int64_t ntiles = M.tiles_i * M.tiles_j;
 
-  push_faces<GX, GY, kDebug>(R, e, par, M.tiles_i);
+  push_faces<GX, GY, kDebug>(R, e, par, M.tiles_i, 32, push_group);
 
   // ---------------- phase 2: tiles from the shared counter
   Sten2d S{R.z, R.out, nx, ny, ldz, R.ldo, R.sx, R.sy, R.x0, R.y0, R.dx, R.dy};
@@ -852,6 +853,10 @@ int gmt_fused_stencil2d_f64(const gmt_halo2d_rank* ranks_dev, int n_ranks, int64
   const char* ord = getenv("GMT_FUSED_ORDER");
   const bool ws = gx && !gy && !oneshot;
   int tj_flags = tj | ((!ws && !(ord && ord[0] == 'i')) ? (1 << 16) : 0);
+  {
+    const char* pp = getenv("GMT_PUSH_PIPELINE");
+    if (!ws && pp && pp[0] == '0') tj_flags |= 1 << 17;   // A/B knob: export without the software pipeline
+  }
   if (ws) {   // tuning knobs of the dim-0 export (tools/dim0_variants.py): chunks per fence, exporting CTAs
     const char* pg = getenv("GMT_PUSH_GROUP");
     const char* pc = getenv("GMT_PUSH_CTAS");

@@ -1,9 +1,9 @@
 #!/bin/bash
-# One GPU-box call for N GPUs: tests, bench (both arms), peer bandwidth, sweeps, cross-GPU ncu capture.
-#   scripts/run_n.sh N [what...]      what: pytest bench peer sweep ncu   (default: all)
+# One GPU-box call for N GPUs: tests, bench (both arms), peer bandwidth, sweeps, dim-0 tuning variants.
+#   scripts/run_n.sh N [what...]      what: pytest bench peer sweep variants exch   (default: pytest bench peer sweep)
 set -u
 N=${1:-2}; shift || true
-WHAT=${*:-pytest bench peer sweep ncu}
+WHAT=${*:-pytest bench peer sweep}
 OUT=gpurun_out/r2
 mkdir -p $OUT
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
@@ -34,8 +34,5 @@ for w in $WHAT; do
     exch)
       timeout 900 $TR benchmarks/sweep.py --only exchanges --out $OUT/sweep_exch_n$N.jsonl > $OUT/sweep_exch_n$N.log 2>&1
       echo "exch rc=$?"; grep halo_exchange $OUT/sweep_exch_n$N.log ;;
-    ncu)
-      timeout 240 $TR --no-python tools/ncu_rank0.sh $OUT/cross_n$N python tools/profile_cross.py > $OUT/ncu_cross_n$N.log 2>&1
-      echo "ncu rc=$?"; tail -5 $OUT/ncu_cross_n$N.log ;;
   esac
 done

@@ -3,7 +3,8 @@
 samples land (by opcode and the top instructions) and which memory/synchronisation opcodes the
 kernel contains.  Writes profiles/source_hotspots.md.
 
-    python tools/ncu_hotspots.py [gpurun_out/prof_all.ncu-rep]"""
+    python tools/ncu_hotspots.py [gpurun_out/prof_all.ncu-rep]
+    python tools/ncu_hotspots.py gpurun_out/prof_round2.ncu-rep      (round-2 kernels -> source_hotspots_round2.md)"""
 import collections
 import csv
 import io
@@ -17,6 +18,13 @@ REP = Path(sys.argv[1]) if len(sys.argv) > 1 else ROOT / "gpurun_out" / "prof_al
 KERNELS = [("fused2d_kernel", 3),   # 4th launch = 2x2 virtual ranks in one cooperative launch (real exchange)
            ("fused_dim0_ws_kernel", 1), ("fused1d_kernel", 1),
            ("stencil2d_d1_cluster_kernel", 1), ("stencil1d_tma_kernel", 1), ("daxpy_sum_vec4_kernel", 1)]
+OUT_NAME = "source_hotspots.md"
+if "round2" in REP.name:
+    # exchange alone (2 virtual ranks, 4 MiB strided faces), dim-0 step with ghosts from the inbox, fused 1-D on the
+    # TMA path, daxpy + global sum (n = 48 Mi: third launch), flag-based and LL allgather, two-shot all-reduce
+    KERNELS = [("halo_exchange2d_kernel", 1), ("fused_dim0_ws_kernel", 1), ("fused1d_tma_kernel", 1),
+               ("daxpy_allreduce_kernel", 3), ("gather_kernel", 1), ("gather_ll_kernel", 1), ("axis_sum_allreduce_kernel", 1)]
+    OUT_NAME = "source_hotspots_round2.md"
 MEM = ("LD", "ST", "ATOM", "RED", "MEMBAR", "ERRBAR", "UBLKCP", "UTMA", "SYNCS", "UCGABAR", "NANOSLEEP")
 
 
@@ -67,8 +75,8 @@ def main():
         out.append("Memory / synchronisation opcodes present (static count): " +
                    ", ".join(f"`{op}` x{n}" for op, n in sorted(mem.items())))
         out.append("")
-    (ROOT / "profiles" / "source_hotspots.md").write_text("\n".join(out) + "\n")
-    print(ROOT / "profiles" / "source_hotspots.md")
+    (ROOT / "profiles" / OUT_NAME).write_text("\n".join(out) + "\n")
+    print(ROOT / "profiles" / OUT_NAME)
 
 
 if __name__ == "__main__":

@@ -58,7 +58,10 @@ def main():
     dest.write_text("\n".join(lines) + "\n")
     print(dest)
     # keep the full listing of the two flagship kernels next to the summary
-    for key in ("fused2d_kernelILi2ELi2ELb1", "daxpy_allreduce_kernel", "stencil1d_tma_kernel", "gather_kernel"):
+    # (the verdict of round 1 asked for the cluster kernel's full listing as well; round 2 adds the exchange-only
+    # kernel, the fused 1-D TMA kernel and the LL allgather)
+    for key in ("fused2d_kernelILi2ELi2ELb1", "daxpy_allreduce_kernel", "stencil1d_tma_kernel", "gather_kernel",
+                "stencil2d_d1_cluster_kernel", "halo_exchange2d_kernelILi2ELi2ELb0", "fused1d_tma_kernel", "gather_ll_kernel"):
         for mangled, body in kernels.items():
             if key in mangled:
                 (ROOT / "profiles" / f"sass_{key}.txt").write_text("\n".join(body) + "\n")
