@@ -518,7 +518,8 @@ def test_coverage_map_points_at_real_files_and_tests():
 
 def test_reported_numbers_match_the_committed_records():
     """README.md / BASELINE.md quote the flagship numbers of profiles/bench_n{1,2,4,8}.json: the quoted
-    GLUP/s must be the recorded ones (rounded), and the records must satisfy the bench contract."""
+    GLUP/s must be the recorded ones (rounded), and the records must satisfy the bench contract, carry the
+    same-box library-only arm (vs_baseline) and every component of BASELINE.json's metric."""
     import json
     from pathlib import Path
     root = Path(__file__).resolve().parents[1]
@@ -528,9 +529,20 @@ def test_reported_numbers_match_the_committed_records():
         assert rec["metric"] == "stencil2d_glups" and rec["n_gpus"] == n and rec["warmup"] >= 3 and rec["dtype"] == "fp64"
         assert rec["e2e"]["h2d_bytes_per_step"] > 0 and rec["e2e"]["d2h_bytes_per_step"] > 0
         assert rec["e2e"]["value"] < rec["value"]                      # end to end cannot beat the device time
+        assert rec["e2e"]["value"] > 0.975 * rec["value"]              # ... and the pipelined step is within 2.5% of it
         assert rec["gpu_launches"] == rec["steps"]                     # one fused kernel per step
         assert not set(rec["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
         assert 0.9 < rec["roofline"]["frac_of_measured_copy_peak"] < 1.1
+        assert rec["ghost_mismatch"] == 0
+        arm = rec["baseline_arm"]
+        assert rec["vs_baseline"] == pytest.approx(rec["value"] / arm["value"]) and arm["e2e_ratio"] > 4.0
+        if n > 1:
+            assert rec["vs_baseline"] > 1.1
+        ex = rec["extra"]
+        assert "errors" not in ex
+        for key in ("halo_exchange_us", "daxpy_sum", "allreduce_8KiB_us", "barrier_us", "allgather", "stencil1d_2p27",
+                    "stencil2d_ref_dim0", "stencil2d_ref_dim1", "stencil2d_periodic4"):
+            assert key in ex, key
         quoted = f"{rec['value']:.0f}"
         assert quoted in baseline, f"{quoted} GLUP/s (N={n}) is not in BASELINE.md"
         if n in (1, 8):
