@@ -133,7 +133,70 @@ def case_collectives(rt, args):
         print("collectives ok (multicast: %s)" % pc.has_multicast, flush=True)
 
 
-CASES = {"fused": case_fused, "baseline": case_baseline, "collectives": case_collectives}
+def case_darray(rt, args):
+    """A user's own compute step on distributed arrays: arbitrary data (a function of the GLOBAL
+    indices, nothing analytic about it), DistArray.exchange() / .apply(fn) with fn a torch expression
+    that reaches two cells into the ghosts, checked against the same expression on the global field.
+    Runs on CPUs (library exchange over gloo) and on GPUs (peer-memory exchange kernel) alike."""
+    from gpu_mpi_tests_b200.parallel import decomp
+    from gpu_mpi_tests_b200.parallel.darray import DistArray1D, DistArray2D
+    r, W = rt.rank, rt.world_size
+    dev = rt.device
+    f64 = torch.float64
+
+    def field(gi, gj):   # any function of the global indices
+        return torch.sin(0.37 * gi)[None, :] * torch.cos(0.11 * gj)[:, None] + 1e-3 * gi[None, :] + 2e-3 * gj[:, None]
+
+    def wide_cross(z, gx, gy, nx, ny):   # reaches 2 cells in every decomposed direction
+        c = z[gy:gy + ny, gx:gx + nx]
+        out = -4.0 * c
+        if gx:
+            out = out + z[gy:gy + ny, 0:nx] + z[gy:gy + ny, 2 * gx:2 * gx + nx]
+        if gy:
+            out = out + z[0:ny, gx:gx + nx] + z[2 * gy:2 * gy + ny, gx:gx + nx]
+        return out
+
+    nx, ny = 64, 48
+    for dims in ((0,), (1,), (0, 1)):
+        if dims == (0, 1):
+            px, py = decomp.best_grid(W)
+        else:
+            px, py = (W, 1) if dims == (0,) else (1, W)
+        a = DistArray2D(rt, nx, ny, dims=dims)
+        gx, gy = a.gx, a.gy
+        cx, cy = r % px, r // px
+        gi = torch.arange(-gx, nx + gx, dtype=f64, device=dev) + cx * nx     # global i of every local column incl. ghosts
+        gj = torch.arange(-gy, ny + gy, dtype=f64, device=dev) + cy * ny
+        full = field(gi, gj)
+        a.local.copy_(full)
+        # poison the ghosts that face a neighbour: only the exchange may fill them
+        g = decomp.Grid2D(px, py, r)
+        for side in range(4):
+            if (gx if side < 2 else gy) and g.neighbour(side) >= 0:
+                a.ghost(side).fill_(1e30)
+        got = a.apply(lambda z: wide_cross(z, gx, gy, nx, ny))
+        want = wide_cross(full, gx, gy, nx, ny)
+        err = float((got - want).abs().max())
+        assert err < 1e-12, f"dims {dims}: custom op after exchange differs by {err}"
+        assert torch.equal(a.local, full), f"dims {dims}: exchange changed something other than the live ghosts"
+    a1 = DistArray1D(rt, 1 << 12)
+    n = a1.slab.n_local
+    gi = torch.arange(-2, n + 2, dtype=f64, device=dev) + r * n
+    full = torch.sin(0.37 * gi) + 1e-3 * gi
+    a1.local.copy_(full)
+    if r > 0:
+        a1.local[:2] = 1e30
+    if r < W - 1:
+        a1.local[-2:] = 1e30
+    got = a1.apply(lambda y: y[:-4] + y[4:] - 2.0 * y[2:-2])
+    want = full[:-4] + full[4:] - 2.0 * full[2:-2]
+    assert float((got - want).abs().max()) < 1e-12
+    rt.barrier()
+    if r == 0:
+        print("darray ok", flush=True)
+
+
+CASES = {"darray": case_darray, "fused": case_fused, "baseline": case_baseline, "collectives": case_collectives}
 
 if __name__ == "__main__":
     name = sys.argv[1]

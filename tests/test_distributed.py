@@ -30,6 +30,23 @@ def test_baseline_exchange_gloo(nproc):
     assert "baseline ok" in out
 
 
+@pytest.mark.parametrize("nproc", [2, 4])
+def test_user_compute_step_on_dist_arrays_gloo(nproc):
+    """DistArray.exchange()/apply(fn) with arbitrary data and a user's own stencil (CPU/gloo flavour)."""
+    out = run_workers(nproc, "darray", env_extra={"GMT_FORCE_CPU": "1"})
+    assert "darray ok" in out
+
+
+@pytest.mark.gpu
+def test_user_compute_step_on_dist_arrays_across_gpus():
+    """The same through the peer-memory exchange kernel on real GPUs."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    out = run_workers(n if n in (2, 4, 8) else 2, "darray")
+    assert "darray ok" in out
+
+
 @pytest.mark.gpu
 def test_fused_kernels_across_gpus():
     n = torch.cuda.device_count()
