@@ -36,25 +36,37 @@ struct CollShared {
   double* stage[GMT_COLL_MAX_WORLD];
   uint64_t* flag[GMT_COLL_MAX_WORLD];
   double red[40];
-  int64_t next[2];
+  int64_t next[2];   // [1]: the epoch read by coll_enter
   bool last;
 };
 
+// Prologue of every collective: the descriptor into shared memory, the three peer tables and the
+// epoch.  The table entries and the epoch are fetched straight from global memory in parallel with
+// the descriptor copy (two dependent loads deep, one barrier) instead of descriptor -> tables ->
+// epoch one after the other: every collective here is latency-bound and each level is ~0.5 us.
 __device__ __forceinline__ uint64_t coll_enter(CollShared& S, const gmt_coll_rank* ranks)
 {
+  const gmt_coll_rank* Rg = ranks + blockIdx.y;
   {
-    const uint64_t* s = reinterpret_cast<const uint64_t*>(ranks + blockIdx.y);
+    const uint64_t* s = reinterpret_cast<const uint64_t*>(Rg);
     uint64_t* d = reinterpret_cast<uint64_t*>(&S.R);
     for (int w = threadIdx.x; w < (int)(sizeof(gmt_coll_rank) / 8); w += blockDim.x) d[w] = s[w];
   }
-  __syncthreads();
-  if ((int)threadIdx.x < S.R.world) {
-    S.buf[threadIdx.x] = S.R.peer_buf ? S.R.peer_buf[threadIdx.x] : nullptr;
-    S.stage[threadIdx.x] = S.R.peer_stage ? S.R.peer_stage[threadIdx.x] : nullptr;
-    S.flag[threadIdx.x] = S.R.peer_flag[threadIdx.x];
+  if (threadIdx.x < GMT_COLL_MAX_WORLD) {
+    const int t = threadIdx.x, W = Rg->world;
+    double* const* pb = Rg->peer_buf;
+    double* const* ps = Rg->peer_stage;
+    uint64_t* const* pf = Rg->peer_flag;
+    if (t < W) {
+      S.buf[t] = pb ? pb[t] : nullptr;
+      S.stage[t] = ps ? ps[t] : nullptr;
+      S.flag[t] = pf[t];
+    }
+  } else if (threadIdx.x == GMT_COLL_MAX_WORLD) {
+    S.next[1] = (int64_t)ld_relaxed_sys(Rg->epoch);
   }
   __syncthreads();
-  return ld_relaxed_sys(S.R.epoch) + 1;
+  return (uint64_t)S.next[1] + 1;
 }
 
 // "rank R.rank has reached `round` of epoch e" to every rank (or to one).  Call after a CTA
