@@ -61,6 +61,19 @@ __device__ __forceinline__ void load_rank(RankT& dst, const RankT* src)
   __syncthreads();
 }
 
+// the same, with the epoch fetched straight from global memory beside the descriptor copy (one level of
+// dependent loads less: the exchange-only kernels are a few microseconds long and latency-bound)
+template <typename RankT>
+__device__ __forceinline__ uint64_t load_rank_and_epoch(RankT& dst, const RankT* src, uint64_t* epoch_smem)
+{
+  const uint64_t* s = reinterpret_cast<const uint64_t*>(src);
+  uint64_t* d = reinterpret_cast<uint64_t*>(&dst);
+  for (int w = threadIdx.x; w < (int)(sizeof(RankT) / 8); w += blockDim.x) d[w] = s[w];
+  if (threadIdx.x == blockDim.x - 1) *epoch_smem = ld_relaxed_sys(src->epoch);
+  __syncthreads();
+  return *epoch_smem + 1;
+}
+
 // last CTA of this rank: reset the counters and advance the epoch
 __device__ __forceinline__ void finish_epoch(uint32_t* done, uint64_t* epoch, uint64_t e, int n_counters)
 {
@@ -584,8 +597,8 @@ template <bool kDebug>
 __global__ void __launch_bounds__(64) halo_exchange1d_kernel(const gmt_halo1d_rank* __restrict__ ranks)
 {
   __shared__ gmt_halo1d_rank R;
-  load_rank(R, ranks + blockIdx.y);
-  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  __shared__ uint64_t epoch0;
+  const uint64_t e = load_rank_and_epoch(R, ranks + blockIdx.y, &epoch0);
   const uint64_t e32 = e & 0xffffffffull;
   const int par = (int)(e & 1);
   const int tid = threadIdx.x;
@@ -630,8 +643,8 @@ template <int GX, int GY, bool kDebug>
 __global__ void __launch_bounds__(kStThreads, 2) halo_exchange2d_kernel(const gmt_halo2d_rank* __restrict__ ranks)
 {
   __shared__ gmt_halo2d_rank R;
-  load_rank(R, ranks + blockIdx.y);
-  const uint64_t e = ld_relaxed_sys(R.epoch) + 1;
+  __shared__ uint64_t epoch0;
+  const uint64_t e = load_rank_and_epoch(R, ranks + blockIdx.y, &epoch0);
   const int par = (int)(e & 1);
   const int tid = threadIdx.x;
   const int64_t nx = R.nx, ny = R.ny, ldz = R.ldz;
