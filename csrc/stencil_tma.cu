@@ -537,6 +537,18 @@ int gmt_stencil2d_d1_cluster_f64(int64_t nx, int64_t ny, const double* z, int64_
               "gmt_stencil2d_d1_cluster_f64: bad argument");
   GMT_REQUIRE(nx % 4 == 0 && ldo % 4 == 0 && ldz % 2 == 0 && aligned(z, 16) && aligned(out, 32), GMT_EUNSUPPORTED,
               "gmt_stencil2d_d1_cluster_f64: unsupported shape or alignment");
+  {
+    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+    // another GPU's memory hung the GPU: the source must be a plain device allocation of the current device
+    // (not a peer mapping, an IPC mapping, a symmetric-memory view of another rank, or managed memory).
+    int dev = -1;
+    GMT_CUDA(cudaGetDevice(&dev));
+    cudaPointerAttributes attr;
+    GMT_CUDA(cudaPointerGetAttributes(&attr, z));
+    GMT_REQUIRE(attr.type == cudaMemoryTypeDevice && attr.device == dev, GMT_EUNSUPPORTED,
+                "gmt_stencil2d_d1_cluster_f64: z must be device memory of the current GPU (device %d); "
+                "use the LSU variant for anything else", dev);
+  }
   CUtensorMap map8, map2;
   int rc = encode_tiled_2d(&map8, z, nx, ny + 4, ldz, kC2Box, kC2Ty);
   if (rc) return rc;

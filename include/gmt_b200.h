@@ -162,7 +162,9 @@ int gmt_stencil2d_f64(int dim, int64_t nx, int64_t ny, const double* z, int64_t 
                       int64_t lddz, double scale, int variant, gmt_stream_t stream);
 /* variant 2 of the dim-1 stencil on its own: 2-D TMA tensor-map loads + thread-block clusters
  * of two CTAs; the 4 halo columns between their tiles are fetched once and delivered to both
- * CTAs' shared memory by TMA multicast (no reference counterpart; see csrc/stencil_tma.cu for the shape/alignment requirements)            */
+ * CTAs' shared memory by TMA multicast (no reference counterpart; see csrc/stencil_tma.cu for the shape/alignment
+ * requirements).  z must be a plain device allocation of the current GPU -- the TMA multicast loads read only this
+ * GPU's memory; a peer / IPC / symmetric-memory mapping or managed memory returns GMT_EUNSUPPORTED.            */
 int gmt_stencil2d_d1_cluster_f64(int64_t nx, int64_t ny, const double* z, int64_t ldz, double* out,
                                  int64_t ldo, double scale, gmt_stream_t stream);
 /* cross stencil on a (nx+4, ny+4) array ghosted in both dims:
