@@ -87,6 +87,18 @@ __device__ __forceinline__ bool ld_ll_cell(const uint64_t* cell, uint64_t e32, d
   return true;
 }
 
+// the two halves of that: a raw load (several can be in flight) and the check
+__device__ __forceinline__ void ld_ll_raw(const uint64_t* cell, uint64_t& w0, uint64_t& w1)
+{
+  asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(cell) : "memory");
+}
+__device__ __forceinline__ bool ll_unpack(uint64_t w0, uint64_t w1, uint64_t e32, double& v)
+{
+  if ((w0 >> 32) != e32 || (w1 >> 32) != e32) return false;
+  v = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+  return true;
+}
+
 constexpr int64_t kDefaultSpinLimit = 1LL << 28;  // ~ tens of seconds of polling
 
 // Bounded spin until *flag >= want.  Returns false on expiry (dead / never-launched
