@@ -15,7 +15,7 @@ the 126 MB L2, so no L2 flush is needed between iterations.
 
 `e2e` runs the same step through the public API `Stencil2DWorkload.step_e2e_pipelined()`: every
 step uploads that step's physical-boundary ghost values from pinned host memory, runs the fused
-kernel and copies the error norm to pinned host memory, where the host reads it one call later
+kernel, whose last CTA stores the error norm straight into pinned host memory, where the host reads it one call later
 (`e2e.sync_value`: the synchronous `step_e2e()`, which reads it before the next step starts).
 
 Same-box anchor: the reference arm cannot run here (see `--impl reference`), so the default run

@@ -8,7 +8,8 @@ may be a whole launch ahead of its neighbour -- and `compute-sanitizer` cannot s
 sequential program of ATOMIC actions on shared words, and `explore()` walks every reachable
 interleaving, failing on the first assertion a schedule can break.
 
-Three models, matching csrc/stencil_fused.cu and csrc/collectives.cu:
+Five models, matching csrc/stencil_fused.cu, csrc/collectives.cu and models/stencil2d.py (the last two,
+`ll_allgather_model` and `host_feed_model`, are described at their definitions):
 
 * `halo_model(n_ranks, steps, buffers)`: per step e a rank stores its boundary into each
   neighbour's inbox[e % buffers], publishes e in the neighbour's flag (release), waits until its
@@ -236,6 +237,94 @@ def ll_allreduce_model(n_ranks: int = 2, calls: int = 3, buffers: int = 2, gathe
                 prog.append((f"take{c}[{src}]", take_cell))
         programs.append(prog)
     return W, init, programs
+
+
+# ---------------------------------------------------------------------------- LL-cell allgather (in place)
+def ll_allgather_model(n_ranks: int = 2, calls: int = 3, buffers: int = 2):
+    """In-place allgather of small slices through LL cells (gather_ll_kernel): per call the USER fills the
+    rank's own slot of its buffer; the rank stores that value, tagged with the call number, into
+    cell[c % buffers][its rank] of every PEER's staging area, takes the peers' cells from its own area
+    (tag must EQUAL the call number) and copies each into its OWN user buffer; then the user reads the
+    whole buffer.  Nobody ever writes another rank's user buffer, so there is no entry round -- the
+    checker confirms that the user's reads never see anything but the current call's values, and that
+    one cell set (buffers=1) deadlocks like the all-reduce."""
+    W = n_ranks
+    n_cells = W * buffers * W
+
+    def idx_cell(owner, b, src):
+        return (owner * buffers + b) * W + src
+
+    def idx_buf(r, slot):
+        return n_cells + r * W + slot
+
+    init = tuple([None] * (n_cells + W * W))
+    programs = []
+    for r in range(W):
+        prog = []
+        for c in range(1, calls + 1):
+            def fill(mem, p, r=r, c=c):
+                mem[idx_buf(r, r)] = (r, c)
+            prog.append((f"fill{c}", fill))
+            for k in range(1, W):
+                def push(mem, p, q=(r + k) % W, r=r, c=c):
+                    mem[idx_cell(q, c % buffers, r)] = (r, c)
+                prog.append((f"push{c}->{(r + k) % W}", push))
+            for k in range(1, W):
+                def take(mem, p, src=(r + k) % W, r=r, c=c):
+                    got = mem[idx_cell(r, c % buffers, src)]
+                    if got is None or got[1] != c:
+                        return False          # not there yet -- or gone for good (reported as deadlock)
+                    mem[idx_buf(r, src)] = got
+                prog.append((f"take{c}[{(r + k) % W}]", take))
+            for slot in range(W):
+                def use(mem, p, slot=slot, r=r, c=c):
+                    got = mem[idx_buf(r, slot)]
+                    assert got == (slot, c), f"rank {r} call {c}: slot {slot} holds {got}, expected {(slot, c)}"
+                prog.append((f"use{c}[{slot}]", use))
+        programs.append(prog)
+    return W, init, programs
+
+
+# ---------------------------------------------------------------------------- host-fed sides, pipelined
+def host_feed_model(steps: int = 4, buffers: int = 2, lookahead: int = 1):
+    """The host as one more neighbour (Stencil2DWorkload.step_e2e_pipelined): process 0 is the host
+    with its copy engine, process 1 the stream of fused kernels.  Per step e the host uploads the
+    boundary values into inbox[e % buffers] and then publishes e in the flag word; the kernel of
+    step e waits for flag >= e, reads the inbox (two separate reads, so that an upload can fall
+    between them), and completes.  The host enqueues step e only after it has seen step
+    e - 1 - lookahead complete (lookahead=1: the pipelined call, which waits for the PREVIOUS step's
+    result after enqueuing the current one; lookahead=0: the synchronous call).  Two inboxes by
+    epoch parity are safe with lookahead 1; with a single inbox the checker finds the upload of step
+    e+1 landing between the two reads of step e."""
+    INBOX, FLAG, DONE = 0, buffers, buffers + 1
+    init = tuple([None] * buffers + [0, 0])
+    host, kern = [], []
+    for e in range(1, steps + 1):
+        def may_enqueue(mem, p, e=e):
+            return None if mem[DONE] >= e - 1 - lookahead else False
+        host.append((f"enqueue{e}", may_enqueue))
+
+        def upload(mem, p, e=e):
+            mem[INBOX + e % buffers] = e
+        host.append((f"upload{e}", upload))
+
+        def publish(mem, p, e=e):
+            mem[FLAG] = e
+        host.append((f"flag{e}", publish))
+
+        def wait(mem, p, e=e):
+            return None if mem[FLAG] >= e else False
+        kern.append((f"wait{e}", wait))
+        for half in (0, 1):
+            def read(mem, p, e=e, half=half):
+                got = mem[INBOX + e % buffers]
+                assert got == e, f"kernel of step {e} (read {half}) sees the boundary values of step {got}"
+            kern.append((f"read{e}.{half}", read))
+
+        def done(mem, p, e=e):
+            mem[DONE] = e
+        kern.append((f"done{e}", done))
+    return 2, init, [host, kern]
 
 
 def check(model: Callable, **kw) -> int:

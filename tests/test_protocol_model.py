@@ -56,6 +56,32 @@ def test_gather_between_reductions_must_not_let_senders_run_ahead():
     assert check(ll_allreduce_model, n_ranks=3, calls=3, buffers=2, gather_between="barrier") > 50
 
 
+@pytest.mark.parametrize("n_ranks,calls", [(2, 4), (3, 2)])
+def test_ll_allgather_in_place_needs_no_entry_round(n_ranks, calls):
+    """Small in-place allgathers through LL cells: nobody writes another rank's user buffer, so the user
+    always reads the current call's values although there is no "entered" round; one cell set is not
+    enough (same lapping as the all-reduce)."""
+    from gpu_mpi_tests_b200.utils.protocol_model import ll_allgather_model
+    assert check(ll_allgather_model, n_ranks=n_ranks, calls=calls, buffers=2) > 50
+    with pytest.raises(ProtocolViolation):
+        check(ll_allgather_model, n_ranks=2, calls=3, buffers=1)
+
+
+def test_pipelined_host_feed_needs_two_inboxes():
+    """step_e2e_pipelined(): the host is one step ahead of the kernels.  With the host inbox
+    double-buffered by epoch parity every kernel reads its own step's boundary values; with a single
+    inbox the upload of the next step can land between two reads of the running kernel.  The
+    synchronous call (no look-ahead) is safe with one inbox."""
+    from gpu_mpi_tests_b200.utils.protocol_model import host_feed_model
+    assert check(host_feed_model, steps=5, buffers=2, lookahead=1) > 20
+    assert check(host_feed_model, steps=4, buffers=1, lookahead=0) > 10
+    with pytest.raises(ProtocolViolation, match="sees the boundary values of step"):
+        check(host_feed_model, steps=3, buffers=1, lookahead=1)
+    # two steps of look-ahead would break parity double-buffering as well
+    with pytest.raises(ProtocolViolation, match="sees the boundary values of step"):
+        check(host_feed_model, steps=4, buffers=2, lookahead=2)
+
+
 def test_checker_reports_deadlock():
     from gpu_mpi_tests_b200.utils.protocol_model import explore
     never = ("wait", lambda mem, p: False)
