@@ -125,6 +125,17 @@ __device__ __forceinline__ void coll_finish(CollShared& S, uint64_t e)
 }
 
 // weak (unqualified) multimem.st: ordering comes from the fence + flag that follow anyway
+// A vector longer than the staging area holds (the raw entry points cannot see stage_cap from the host):
+// write nothing, say so in the status word, still advance the epoch so that the rank stays in step.
+// CTA-uniform, and every rank takes the same branch (same n, same stage_cap).
+__device__ __forceinline__ bool coll_too_big(CollShared& S, uint64_t e, int64_t n)
+{
+  if (n <= S.R.stage_cap) return false;
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(S.R.status, kStatusTooBig);
+  if (arrive_last(S, S.R.done + 2, false)) coll_finish(S, e);
+  return true;
+}
+
 __device__ __forceinline__ void multimem_st_32B_weak(double* mc, const double4_t& v)
 {
   const float4* f = reinterpret_cast<const float4*>(&v);
@@ -409,6 +420,7 @@ __global__ void __launch_bounds__(kCollThreads, 2)
 {
   __shared__ CollShared S;
   const uint64_t e = coll_enter(S, ranks);
+  if (coll_too_big(S, e, n)) return;
   const double* in = S.R.in;
   const int64_t stride = (int64_t)gridDim.x * kCollThreads;
   for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += stride) ll_push(S, e, i, in[i]);
@@ -421,6 +433,7 @@ __global__ void __launch_bounds__(kCollThreads, 2)
 {
   __shared__ CollShared S;
   const uint64_t e = coll_enter(S, ranks);
+  if (coll_too_big(S, e, n)) return;
   double* mine = S.stage[S.R.rank] + (int64_t)(e & 1) * S.R.stage_cap;
   const double* in = S.R.in;
   for (int64_t i = (int64_t)blockIdx.x * kCollThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kCollThreads)
@@ -467,7 +480,8 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   __shared__ CollShared S;
   __shared__ double tile[16][33];
   const uint64_t e = coll_enter(S, ranks);
-  const bool ll = n_out * S.R.world <= kLLMaxCells && n_out <= S.R.stage_cap;
+  if (coll_too_big(S, e, n_out)) return;
+  const bool ll = n_out * S.R.world <= kLLMaxCells;
   double* mine = S.stage[S.R.rank] + (int64_t)(e & 1) * S.R.stage_cap;
   const double* z = S.R.in;
   double* out = S.R.out;

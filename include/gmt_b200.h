@@ -324,9 +324,10 @@ int64_t gmt_halo2d_flag_count(int side, int64_t nx, int64_t ny);
  *
  * Sizes: a staging area is gmt_coll_stage_bytes(world, stage_cap) bytes; stage_cap must be at least
  * gmt_coll_min_stage_cap() (= 2048: gmt_daxpy_allreduce_f64 stores one cell per CTA, up to 2048).
- * The raw entry points cannot see stage_cap from the host; a kernel that would need more cells
- * than the descriptor's stage_cap writes nothing, sets bit 0x1000 in the status word and (daxpy)
- * returns NaN.  The engines and the Python layer check sizes on the host and return GMT_ETOOBIG. */
+ * The raw entry points cannot see stage_cap from the host; a kernel that would need more staging
+ * doubles or cells than the descriptor's stage_cap (all-reduce / axis-sum n, LL allgather slice,
+ * daxpy partial cells) writes nothing, sets bit 0x1000 in the status word, still advances the
+ * epoch, and (daxpy) returns NaN.  The engines and the Python layer check sizes on the host and return GMT_ETOOBIG. */
 size_t gmt_coll_stage_bytes(int world, int64_t stage_cap);
 int64_t gmt_coll_min_stage_cap(void);
 int64_t gmt_coll_ll_gather_max(void);   /* largest slice (doubles) gmt_allgather_f64 takes in LL mode */

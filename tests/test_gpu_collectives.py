@@ -64,7 +64,7 @@ def test_allgather_from_separate_source(dev, mode):
     pc.check_status()
 
 
-def test_ll_gather_reports_a_too_small_staging_area(dev):
+def test_too_small_staging_area_is_reported_not_overrun(dev):
     """The raw entry points cannot see stage_cap from the host: a call that needs more LL cells than
     the descriptor provides must write nothing out of bounds and say so in the status word."""
     from gpu_mpi_tests_b200.ops._lib import lib
@@ -78,6 +78,17 @@ def test_ll_gather_reports_a_too_small_staging_area(dev):
     with pytest.raises(CollectiveTimeout, match="stage_cap"):
         pc.check_status()
     assert all(float(pc.buffer(r).max()) == -1.0 for r in range(world))
+    # the all-reduce entry points say so as well instead of overrunning the staging area
+    for algo in (0, 1, 3):
+        pc2 = PeerCollectives(VirtualSpace(world, dev), stage_cap=2048, spin_limit=1 << 20)
+        vec = {r: torch.ones(4096, dtype=F64, device=dev) for r in range(world)}
+        pc2.bind({r: (vec[r], vec[r], None) for r in range(world)})
+        lib.gmt_allreduce_f64(pc2._ranks_dev.data_ptr(), world, 4096, algo, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        with pytest.raises(CollectiveTimeout, match="stage_cap"):
+            pc2.check_status()
+        assert all(float(vec[r].min()) == float(vec[r].max()) == 1.0 for r in range(world))
+        assert pc2.epochs() == [1] * world          # the ranks stay in step
 
 
 @pytest.mark.parametrize("algo", ["ll", "one_shot", "two_shot"])
