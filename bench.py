@@ -22,7 +22,10 @@ Same-box anchor: the reference arm cannot run here (see `--impl reference`), so 
 ALSO times the library-only restatement of the reference's algorithm (`gpu_mpi_tests_b200.baseline`:
 pack kernels, NCCL send/recv, unpack kernels, device-wide syncs, un-fused stencil -- the same code
 `--impl baseline` runs alone) in the same process on the same GPUs: `vs_baseline` = value / that
-arm's value, details in `baseline_arm`.
+arm's value, details in `baseline_arm`.  (The library arm's device-timed step is exchange + stencil
+only, as in the reference, which computes the error norm once after its loop; the fused step carries
+the in-kernel error norm, ~13 us -- which is why `vs_baseline` is 0.99 on one GPU, where there is no
+exchange to win.  Both arms' end-to-end steps deliver the error norm to the host every step.)
 
 `extra` carries the rest of BASELINE.json's metric at this N, every row for both arms ("fused" =
 peer-memory kernels, "lib" = NCCL / torch library calls), device-timed, max over ranks:
