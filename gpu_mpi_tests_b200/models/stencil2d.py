@@ -80,6 +80,7 @@ class Stencil2DWorkload:
         else:
             raise ValueError("impl must be fused or baseline")
         self._host_bc = None
+        self.last_e2e_err = None     # err_norm delivered to the host by the last end-to-end call
         self.host_fed = bool(host_fed) and impl == "fused"
 
     # ------------------------------------------------------------------ setup / step
@@ -264,9 +265,16 @@ class Stencil2DWorkload:
                     box[par].copy_(h, non_blocking=True)
                 for r in self.ranks:
                     self.plan.publish_host_sides_by_copy(r, slot)   # copy engine: needs no SM slot
+            if self.with_err:
+                # the kernel's last CTA stores the error word straight into pinned host memory (mapped into
+                # the device's address space): no device-to-host copy node behind the kernel
+                self.plan.host_result_slots()
+                self.plan.step(result_slot=slot)
+                main.wait_stream(side)
+                return
             self.plan.step()
             main.wait_stream(side)
-            for k, r in enumerate(self.ranks):   # straight from the kernel's result word to pinned memory
+            for k, r in enumerate(self.ranks):
                 self._err_host2[slot][k:k + 1].copy_(self.err_sumsq(r), non_blocking=True)
             return
         if self._bc_total:
@@ -336,7 +344,11 @@ class Stencil2DWorkload:
             self._warmed = True
         if cuda:
             torch.cuda.current_stream().synchronize()
-        return self._result(self._err_host)
+        if self.host_fed and self.with_err:
+            self.last_e2e_err = self._result(self.plan.host_result_slots()[0][:, 0])
+        else:
+            self.last_e2e_err = self._result(self._err_host)
+        return self.last_e2e_err
 
     def step_e2e_pipelined(self):
         """The same step for a loop that can live with a result that lags ONE step: enqueue this
@@ -383,7 +395,8 @@ class Stencil2DWorkload:
         if self._pipe_calls < 2:
             return None
         self._pipe_events[prev].synchronize()
-        return self._result(results[prev][:, 0])
+        self.last_e2e_err = self._result(results[prev][:, 0])
+        return self.last_e2e_err
 
     def e2e_flush(self):
         """Wait for the step enqueued by the last step_e2e_pipelined() call; returns its err_norm
@@ -396,7 +409,8 @@ class Stencil2DWorkload:
             return None
         self._pipe_events[last].synchronize()
         torch.cuda.current_stream().wait_stream(self._side_stream)
-        return self._result(self.plan.host_result_slots()[last][:, 0])
+        self.last_e2e_err = self._result(self.plan.host_result_slots()[last][:, 0])
+        return self.last_e2e_err
 
     # ------------------------------------------------------------------ validation
     def analytic(self, rank: int) -> torch.Tensor:
