@@ -71,9 +71,25 @@ __device__ __forceinline__ uint64_t coll_enter(CollShared& S, const gmt_coll_ran
 
 // "rank R.rank has reached `round` of epoch e" to every rank (or to one).  Call after a CTA
 // barrier: the release is cumulative over what the CTA wrote before the barrier.
-__device__ __forceinline__ void signal_all(CollShared& S, int round, uint64_t e)
+// publishes = true: the signal makes data this grid wrote visible -- a release.  In a multi-CTA grid
+// arrive_last has just executed its system fences on thread 0 of the last CTA, so that thread stores all the
+// flags itself, relaxed (fence + relaxed store is a release pattern; a second MEMBAR.SYS costs ~1.4 us).  A
+// single-CTA grid has no such fence: its threads store one flag each with release semantics (the CTA barrier
+// before makes the release cumulative over what the CTA wrote).  publishes = false: the signal only says
+// "I am in this call" (entry round) -- nothing of this kernel's to publish: relaxed, one flag per thread.
+__device__ __forceinline__ void signal_all(CollShared& S, int round, uint64_t e, bool publishes = true)
 {
-  if ((int)threadIdx.x < S.R.world) st_release_sys(S.flag[threadIdx.x] + round * kRoundStride + S.R.rank, e);
+  const int W = S.R.world;
+  if (publishes && gridDim.x > 1) {
+    if (threadIdx.x == 0)
+      for (int p = 0; p < W; ++p) st_relaxed_sys(S.flag[p] + round * kRoundStride + S.R.rank, e);
+    return;
+  }
+  if ((int)threadIdx.x < W) {
+    uint64_t* f = S.flag[threadIdx.x] + round * kRoundStride + S.R.rank;
+    if (publishes) st_release_sys(f, e);
+    else st_relaxed_sys(f, e);
+  }
 }
 __device__ __forceinline__ void signal_one(CollShared& S, int dst, int round, uint64_t e)
 {
@@ -170,8 +186,8 @@ __global__ void __launch_bounds__(kCollThreads, 2)
   const bool all = root < 0;
   // round 0: nobody's buffer may be written before its owner has entered this epoch
   if (blockIdx.x == 0) {
-    if (all) signal_all(S, 0, e);
-    else if (r == root) signal_all(S, 0, e);
+    if (all) signal_all(S, 0, e, false);
+    else if (r == root) signal_all(S, 0, e, false);
   }
   if (all) wait_all(S, 0, e);
   else if (r != root) wait_one(S, root, 0, e);
