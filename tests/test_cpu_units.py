@@ -547,3 +547,32 @@ def test_reported_numbers_match_the_committed_records():
         assert quoted in baseline, f"{quoted} GLUP/s (N={n}) is not in BASELINE.md"
         if n in (1, 8):
             assert quoted in readme, f"{quoted} GLUP/s (N={n}) is not in README.md"
+
+
+def test_baseline_tables_are_the_ones_generated_from_the_records():
+    """BASELINE.md section 4a is generated by tools/baseline_rows.py from profiles/bench_n*.json and
+    profiles/sweep_n*.jsonl: every generated table row must be in the document verbatim."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    out = subprocess.run([sys.executable, str(root / "tools" / "baseline_rows.py")], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    doc = (root / "BASELINE.md").read_text()
+    rows = [ln for ln in out.stdout.splitlines() if ln.startswith("|")]
+    assert len(rows) > 30
+    missing = [ln for ln in rows if ln not in doc]
+    assert not missing, "BASELINE.md section 4a is out of date with the records:\n" + "\n".join(missing[:5])
+
+
+def test_periodic_grid_neighbours_are_mutual_and_everybody_has_four():
+    from gpu_mpi_tests_b200.parallel.decomp import Grid2D
+    for px, py in ((1, 1), (2, 1), (4, 2), (3, 3), (3, 4)):
+        for r in range(px * py):
+            g = Grid2D(px, py, r, periodic=True)
+            nb = g.neighbours()
+            assert all(0 <= n < px * py for n in nb) and g.physical_mask() == 0
+            for side, n in enumerate(nb):
+                assert Grid2D(px, py, n, periodic=True).neighbour(side ^ 1) == r
+    g = Grid2D(4, 2, 0)
+    assert g.neighbours() == [-1, 1, -1, 4] and g.physical_mask() == 0b0101
